@@ -1,0 +1,85 @@
+// rac_common.cuh — shared host/device plumbing of librac_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <atomic>
+#include "../../include/rac.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "librac_b200 is written for sm_100a (B200) only"
+#endif
+
+namespace rac {
+
+// ---- error plumbing ---------------------------------------------------------
+void set_error(const char* fmt, ...);
+extern std::atomic<long long> g_launches;
+
+#define RAC_CUDA_CHECK(expr)                                                        \
+    do {                                                                            \
+        cudaError_t _e = (expr);                                                    \
+        if (_e != cudaSuccess) {                                                    \
+            rac::set_error("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e),  \
+                           __FILE__, __LINE__);                                     \
+            return RAC_E_CUDA;                                                      \
+        }                                                                           \
+    } while (0)
+
+#define RAC_REQUIRE(cond, ...)                                                      \
+    do {                                                                            \
+        if (!(cond)) {                                                              \
+            rac::set_error(__VA_ARGS__);                                            \
+            return RAC_E_INVALID;                                                   \
+        }                                                                           \
+    } while (0)
+
+// Call after every kernel launch: counts it and surfaces launch-configuration errors.
+#define RAC_LAUNCHED()                                                              \
+    do {                                                                            \
+        rac::g_launches.fetch_add(1, std::memory_order_relaxed);                    \
+        RAC_CUDA_CHECK(cudaGetLastError());                                         \
+    } while (0)
+
+// ---- device-resident mesh table ---------------------------------------------
+struct MeshDev {
+    const float*   verts;     // V*3 object-frame positions
+    const int*     faces;     // T*3 vertex indices
+    const float*   fnormals;  // T*3 unit face normals (object frame), 0 for degenerate faces
+    const float*   uv;        // V*2 or nullptr
+    const uchar4*  vcolor;    // V   or nullptr (RGBA8, COLOR_0)
+    const uchar4*  tex;       // mip chain, level 0 first (RGBA8, sRGB-encoded) or nullptr
+    int V, T;
+    int tw, th, nmips;
+    float base_color[4];
+    float metallic, roughness;
+};
+
+constexpr int kMaxMeshes = 4096;
+const MeshDev* mesh_table_dev();                  // device pointer to MeshDev[kMaxMeshes]
+int mesh_host_info(rac_mesh_t h, int* V, int* T); // 0 ok
+
+// ---- small device helpers ---------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ unsigned warp_max(unsigned v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = max(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_maxf(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+}  // namespace rac

@@ -1,0 +1,67 @@
+// raster.cuh — data layout shared by the render kernels (setup -> band raster -> finalize).
+//
+// Pipeline spec ("RS", restated from SURVEY.md §8a R1-R9; the CPU oracle in oracle/raster_ref.c
+// implements the same spec independently):
+//   RS-V  vertex:  pc = R p + t (fma chain x,y,z order), iz = 1/zc, u = fma(fx, xc*iz, cx),
+//         v = fma(fy, yc*iz, cy); snapped to 1/256 px: X = rint(256 u), Y = rint(256 v).
+//         A triangle with any vertex zc < znear or |u|,|v| > 16384 px is dropped (no clipping).
+//   RS-T  triangle: area2 = (X1-X0)(Y2-Y0) - (X2-X0)(Y1-Y0) in int64; front-facing iff
+//         area2 < 0 (GL CCW after the v-flip, R4); v1<->v2 are swapped so the interior is E>=0.
+//   RS-C  coverage: 4 samples per pixel at subpixel (96,32),(224,96),(32,160),(160,224)/256,
+//         exact int64 edge functions, top-left fill rule.
+//   RS-Z  depth: 1/z is affine in screen space: iz(P) = fma(gy, Py-Y0, fma(gx, Px-X0, iz0));
+//         d = fma(-fn/(f-n), iz, f/(f-n)); d24 = rint(d * (2^24-1)); GL_LESS against 0xFFFFFF;
+//         ties broken by the lower triangle index (GL's in-order rasterisation).
+//   RS-S  shading once per (pixel, triangle) at the pixel centre, pyrender mesh.frag
+//         metallic-roughness BRDF with a head-light spot (R7), gamma 1/2.2, RGBA8 round-to-nearest.
+//   RS-R  resolve: colour = (sum of the 4 samples' RGBA8 + 2) >> 2 (background 0); depth = sample 0.
+//   RS-D  depth readback (R6): d = d24/(2^24-1); zn = 2d-1; depth = 2nf / ((f+n) - zn (f-n)) in f32.
+//   RS-N  per-image max-normalisation of the 8-bit colour (R9).
+#pragma once
+#include "rac_common.cuh"
+
+namespace rac {
+
+constexpr int kSubpix = 256;          // 8 subpixel bits
+constexpr float kGuardPx = 16384.0f;  // guard band in pixels
+constexpr unsigned kDepthMax = 0xFFFFFFu;
+constexpr unsigned long long kKeyEmpty = ~0ull;
+
+// per-image accumulators, zeroed at the start of every call
+struct ImgStats {
+    unsigned nsurv;      // triangles that survived setup
+    unsigned qmax;       // max resolved 8-bit colour value (R9)
+    unsigned dcount;     // #pixels with depth > 0.01      (normalize_depth mask)
+    unsigned dmax_bits;  // float bits of max depth (depth >= 0 so uint order == float order)
+    double dsum, dsumsq; // over depth > 0.01
+    double gsum, gsumsq; // over every gt value (normalize_img)
+    double pad[2];
+};
+static_assert(sizeof(ImgStats) == 64, "ImgStats must be 64 B");
+
+// One record per (image, triangle) that survived setup: 3 x 16 B.
+//  q0 = {X0, Y0, X1, Y1}   q1 = {X2, Y2, iz0, gx}   q2 = {gy, nx, ny, nz}
+struct TriRec {
+    int4 q0, q1, q2;
+};
+
+struct RenderWs {
+    ImgStats* stats;
+    int* mesh_ids;
+    unsigned* surv_y;    // [B][maxT] ymin | ymax<<16 (pixels)
+    unsigned* surv_tri;  // [B][maxT] triangle index
+    int4* recs;          // [B][maxT][3]
+    unsigned* rgba;      // [B][H][W] resolved RGBA8
+    float* depth;        // [B][H][W] metric depth (may alias the caller's depth output)
+    size_t total;
+};
+
+struct SceneConsts {
+    float znear, zfar;
+    float c0, c1;            // d = c0 - c1 * iz  (f/(f-n), fn/(f-n))
+    float rb_num, rb_sum, rb_diff;  // depth readback constants 2nf, f+n, f-n (f32, numpy weak-scalar casts)
+    float las, lao;          // spot-light angle scale / offset
+    float intensity, ambient;
+};
+
+}  // namespace rac

@@ -1,0 +1,13 @@
+"""rac — the B200-native render-and-compare core (ctypes over librac_b200.so).
+
+Public surface used by the shadow modules one directory up (renderer.py, data_loaders.py,
+rotation_representation.py, loss.py, se3_helpers.py) and by callers that want to stay on the
+device: rac.render_batch_device, rac.render_concat_device, rac.assemble_input_device,
+rac.mesh (load / procedural / device cache), rac.ops (autograd functions).
+"""
+from . import _lib, mesh, ops
+from ._lib import RacError, launch_count, lib
+from .render import assemble_input_device, render_batch_device, render_concat_device
+
+__all__ = ["_lib", "mesh", "ops", "RacError", "launch_count", "lib", "assemble_input_device",
+           "render_batch_device", "render_concat_device"]

@@ -1,0 +1,212 @@
+"""-m gpu: the CUDA kernels of steps 3-5 (through the C ABI, via the drop-in Python modules)
+against the pinned oracle (oracle/pose_loss_ref.py) and the reference-generated golden vectors.
+Tolerances: forward 1e-5 relative (north_star), gradients 2e-4 relative (the reference's own
+fp32 autograd carries ~1e-4 noise in the exp-map / SVD backward; the kernels run in fp64)."""
+import contextlib
+import io
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import pose_loss_ref as R
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "pose_loss_golden.npz")
+ROTS = [("6D", 9), ("SVD", 12), ("3D", 6)]
+
+
+@pytest.fixture(scope="module")
+def gold():
+    return {k: v for k, v in np.load(GOLD).items()}
+
+
+@pytest.fixture(scope="module")
+def mods():
+    import loss
+    import rotation_representation as rr
+    return rr, loss
+
+
+def cu(a):
+    return torch.from_numpy(np.array(a)).cuda()
+
+
+def quiet():
+    return contextlib.redirect_stdout(io.StringIO())
+
+
+@pytest.mark.parametrize("rot,D", ROTS)
+def test_pose_update_golden(gold, mods, rot, D):
+    rr, _ = mods
+    y, T_in, Ks = cu(gold[f"y_{rot}"]), cu(gold["T_in"]), torch.from_numpy(gold["Ks"])
+    out = rr.calculate_T_CO_pred(y, T_in, rot, Ks)
+    assert out.dtype == torch.float32 and out.is_cuda and out.shape == (len(y), 4, 4)
+    np.testing.assert_allclose(out.cpu().numpy(), gold[f"Tnew_{rot}_f32"], rtol=1e-5, atol=1e-6)
+    out64 = rr.calculate_T_CO_pred(y, T_in.double(), rot, Ks)       # Q6
+    np.testing.assert_allclose(out64.cpu().numpy(), gold[f"Tnew_{rot}_f64"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_array_equal(out[:, 3].cpu().numpy(), np.tile([0, 0, 0, 1], (len(y), 1)))   # Q3
+
+
+@pytest.mark.parametrize("rot,D", ROTS)
+def test_losses_and_grads_golden(gold, mods, rot, D):
+    rr, ls = mods
+    y = cu(gold[f"y_{rot}"]).requires_grad_(True)
+    T_in, T_gt, T_prev, pts = (cu(gold[k]) for k in ("T_in", "T_gt", "T_prev", "pts"))
+    Ks = torch.from_numpy(gold["Ks"])
+    T_new = rr.calculate_T_CO_pred(y, T_in, rot, Ks)
+    (gy,) = torch.autograd.grad((T_new * cu(gold[f"W_{rot}"])).sum(), y, retain_graph=True)
+    np.testing.assert_allclose(gy.cpu().numpy(), gold[f"gy_{rot}"], rtol=2e-4, atol=1e-5)
+    with quiet():
+        losses = {
+            "l1": ls.compute_ADD_L1_loss(T_gt, T_new, pts),
+            "l1_ps": ls.compute_ADD_L1_loss(T_gt, T_new, pts, use_batch_mean=False),
+            "l2": ls.compute_ADD_L2_loss(T_gt, T_new, pts),
+            "l2_ps": ls.compute_ADD_L2_loss(T_gt, T_new, pts, use_batch_mean=False),
+            "dis": ls.compute_disentangled_ADD_L1_loss(T_new, T_gt, pts),
+            "dis_swapped": ls.compute_disentangled_ADD_L1_loss(T_gt, T_new, pts),
+            "scaled": ls.compute_scaled_disentl_ADD_L1_loss(T_prev, T_new, T_gt, pts),
+        }
+    for k, v in losses.items():
+        np.testing.assert_allclose(v.detach().cpu().numpy(), gold[f"{k}_{rot}"], rtol=1e-5, atol=1e-7, err_msg=k)
+        if v.dim() == 0:
+            (g,) = torch.autograd.grad(v, y, retain_graph=True)
+            np.testing.assert_allclose(g.cpu().numpy(), gold[f"g_{k}_{rot}"], rtol=2e-4, atol=1e-6, err_msg=k)
+
+
+@pytest.mark.parametrize("rot,D", ROTS)
+@pytest.mark.parametrize("B,N", [(1, 1), (3, 17), (64, 1000), (257, 333)])
+def test_against_oracle_seeded(mods, rot, D, B, N):
+    rr, ls = mods
+    g = torch.Generator().manual_seed(1000 * B + N)
+    y0 = 0.1 * torch.randn(B, D, generator=g)
+    if rot == "6D":
+        y0[:, 0] += 1; y0[:, 4] += 1
+    if rot == "SVD":
+        y0[:, 0] += 1; y0[:, 4] += 1; y0[:, 8] += 1
+    y0[:, D - 1] = 1 + 0.05 * torch.randn(B, generator=g)
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "golden"))
+    from make_pose_loss_golden import random_pose
+    T_in, T_gt, T_prev = random_pose(g, B), random_pose(g, B), random_pose(g, B)
+    pts = torch.randn(B, N, 3, generator=g) * 0.3
+    Ks = torch.tensor([[444.44, 0, 160.0], [0, 444.44, 160.0], [0, 0, 1]]).repeat(B, 1, 1)
+    yc = y0.clone().requires_grad_(True)
+    yg = y0.clone().cuda().requires_grad_(True)
+    Tc = R.pose_update(yc, T_in, rot, Ks)
+    Tg = rr.calculate_T_CO_pred(yg, T_in.cuda(), rot, Ks)
+    np.testing.assert_allclose(Tg.detach().cpu().numpy(), Tc.detach().numpy(), rtol=1e-5, atol=1e-6)
+    with quiet():
+        pairs = {
+            "l1": (R.add_l1(T_gt, Tc, pts), ls.compute_ADD_L1_loss(T_gt.cuda(), Tg, pts.cuda())),
+            "l2": (R.add_l2(T_gt, Tc, pts), ls.compute_ADD_L2_loss(T_gt.cuda(), Tg, pts.cuda())),
+            "dis": (R.disentangled(Tc, T_gt, pts), ls.compute_disentangled_ADD_L1_loss(Tg, T_gt.cuda(), pts.cuda())),
+            "dis_swapped": (R.disentangled(T_gt, Tc, pts), ls.compute_disentangled_ADD_L1_loss(T_gt.cuda(), Tg, pts.cuda())),
+            "scaled": (R.disentangled_scaled(T_prev, Tc, T_gt, pts),
+                       ls.compute_scaled_disentl_ADD_L1_loss(T_prev.cuda(), Tg, T_gt.cuda(), pts.cuda())),
+        }
+    for k, (a, b) in pairs.items():
+        np.testing.assert_allclose(b.item(), a.item(), rtol=1e-5, err_msg=k)
+        (ga,) = torch.autograd.grad(a, yc, retain_graph=True)
+        (gb,) = torch.autograd.grad(b, yg, retain_graph=True)
+        scale = max(ga.abs().max().item(), 1e-8)
+        np.testing.assert_allclose(gb.cpu().numpy(), ga.numpy(), rtol=5e-4, atol=2e-4 * scale, err_msg=k)
+    # per-sample variants
+    a = R.add_l1(T_gt, Tc, pts, False)
+    b = ls.compute_ADD_L1_loss(T_gt.cuda(), Tg, pts.cuda(), use_batch_mean=False)
+    assert b.shape == (B,)
+    np.testing.assert_allclose(b.detach().cpu().numpy(), a.detach().numpy(), rtol=1e-5, atol=1e-8)
+
+
+def test_rotation_heads_are_rotations(mods):
+    rr, _ = mods
+    g = torch.Generator().manual_seed(5)
+    for fn, D in ((rr.compute_rotation_matrix_from_ortho6d, 6), (rr.symmetric_orthogonalization, 9), (rr.vec_3d_to_SO3, 3)):
+        x = torch.randn(512, D, generator=g).cuda()
+        Rm = fn(x).double()
+        eye = torch.eye(3, dtype=torch.float64, device="cuda").expand(512, 3, 3)
+        assert torch.allclose(Rm @ Rm.transpose(1, 2), eye, atol=5e-6)
+        assert torch.allclose(torch.det(Rm), torch.ones(512, dtype=torch.float64, device="cuda"), atol=5e-6)
+
+
+def test_rotation_heads_vs_oracle_and_known_answers(gold, mods):
+    rr, _ = mods
+    Rm = rr.vec_3d_to_SO3(cu(gold["v3"]))
+    np.testing.assert_allclose(Rm.cpu().numpy(), gold["R_v3"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_array_equal(Rm[1].cpu().numpy(), np.eye(3, dtype=np.float32))   # Q8: clamped zero vector
+    g = torch.Generator().manual_seed(6)
+    x6 = torch.randn(64, 6, generator=g)
+    np.testing.assert_allclose(rr.compute_rotation_matrix_from_ortho6d(x6.cuda()).cpu().numpy(), R.rot_6d(x6).numpy(), rtol=1e-5, atol=1e-6)
+    x6b = torch.randn(4, 5, 6, generator=g)      # leading dims, like the reference's `...`
+    assert rr.compute_rotation_matrix_from_ortho6d(x6b.cuda()).shape == (4, 5, 3, 3)
+    x9 = torch.randn(64, 9, generator=g)
+    x9d = x9.double()
+    np.testing.assert_allclose(rr.symmetric_orthogonalization(x9.cuda()).cpu().numpy(), R.rot_svd(x9d).float().numpy(), rtol=1e-5, atol=2e-6)
+
+
+def test_svd_head_gradient_vs_fp64_oracle(mods):
+    rr, _ = mods
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(128, 9, generator=g)
+    W = torch.randn(128, 3, 3, generator=g)
+    xc = x.double().requires_grad_(True)
+    (ga,) = torch.autograd.grad((R.rot_svd(xc) * W.double()).sum(), xc)
+    xg = x.cuda().requires_grad_(True)
+    (gb,) = torch.autograd.grad((rr.symmetric_orthogonalization(xg) * W.cuda()).sum(), xg)
+    err = (gb.cpu().double() - ga).abs().max(dim=1).values / ga.abs().max(dim=1).values.clamp(min=1e-6)
+    assert err.median() < 1e-5 and err.max() < 5e-3, (err.median(), err.max())
+
+
+def test_transform_pts(gold, mods):
+    _, ls = mods
+    out = ls.transform_pts(cu(gold["T_multi"]), cu(gold["pts"]))
+    assert out.shape == gold["xf_multi"].shape
+    np.testing.assert_allclose(out.cpu().numpy(), gold["xf_multi"], rtol=1e-5, atol=1e-6)
+    T = cu(gold["T_gt"]).requires_grad_(True)
+    p = cu(gold["pts"]).requires_grad_(True)
+    o = ls.transform_pts(T, p)
+    np.testing.assert_allclose(o.detach().cpu().numpy(), gold["xf_single"], rtol=1e-5, atol=1e-6)
+    W = torch.randn_like(o)
+    gT, gp = torch.autograd.grad((o * W).sum(), (T, p))
+    Tc, pc = torch.from_numpy(gold["T_gt"]).requires_grad_(True), torch.from_numpy(gold["pts"]).requires_grad_(True)
+    gTc, gpc = torch.autograd.grad((R.xform(Tc, pc) * W.cpu()).sum(), (Tc, pc))
+    np.testing.assert_allclose(gT.cpu().numpy(), gTc.numpy(), rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(gp.cpu().numpy(), gpc.numpy(), rtol=1e-4, atol=1e-5)
+    with pytest.raises(ValueError):
+        ls.transform_pts(torch.zeros(2, 4).cuda(), cu(gold["pts"])[:2])
+
+
+def test_error_conventions(mods):
+    rr, ls = mods
+    y = torch.zeros(4, 9).cuda()
+    T = torch.eye(4).repeat(4, 1, 1).cuda()
+    Ks = torch.eye(3).repeat(4, 1, 1)
+    with pytest.raises(AssertionError):
+        rr.calculate_T_CO_pred(y, T, "SVD", Ks)          # wrong width for SVD
+    with pytest.raises(AssertionError):
+        rr.calculate_T_CO_pred(y, T[:3], "6D", Ks)
+    with pytest.raises(AssertionError):
+        rr.calculate_T_CO_pred(y, T, "quat", Ks)          # unknown representation: assert False
+    with pytest.raises(ValueError):
+        rr.so3_exp_map(torch.zeros(4, 4).cuda())
+    with pytest.raises(AssertionError):
+        ls.compute_ADD_L1_loss(T, T[:3], torch.zeros(4, 10, 3).cuda())
+
+
+def test_cpu_tensors_are_staged_through_the_gpu(mods):
+    rr, ls = mods
+    g = torch.Generator().manual_seed(8)
+    y = (0.1 * torch.randn(5, 9, generator=g)).requires_grad_(True)
+    y.data[:, 0] += 1; y.data[:, 4] += 1; y.data[:, 8] = 1
+    from make_pose_loss_golden import random_pose
+    T_in, T_gt = random_pose(g, 5), random_pose(g, 5)
+    pts = torch.randn(5, 40, 3, generator=g)
+    Ks = torch.eye(3).repeat(5, 1, 1) * 400
+    Tn = rr.calculate_T_CO_pred(y, T_in, "6D", Ks)
+    assert Tn.device.type == "cpu"
+    l = ls.compute_ADD_L1_loss(T_gt, Tn, pts)
+    l.backward()
+    assert y.grad is not None and torch.isfinite(y.grad).all()
+    ref = R.add_l1(T_gt, R.pose_update(y.detach(), T_in, "6D", Ks), pts)
+    np.testing.assert_allclose(l.item(), ref.item(), rtol=1e-5)

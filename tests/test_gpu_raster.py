@@ -1,0 +1,251 @@
+"""-m gpu: the CUDA rasteriser + fused input assembly (through the C ABI) against the CPU oracle
+(oracle/raster_ref.c, parity UNPINNED — see its header) on identical synthetic meshes and poses.
+
+Bars (north_star): depth and coverage identical except for at most 0.1% of pixels; where both
+hit, depth within 1e-5 relative; colour within 2/255; assembled input within 1e-5 (abs floor)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import intrinsics, sample_poses
+from oracle import assemble_ref
+from oracle import raster_oracle as ro
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def rac():
+    import rac as _rac
+    return _rac
+
+
+def meshes():
+    from rac import mesh as M
+    return {
+        "ico3": M.icosphere(3),
+        "bumpy5k": M.bumpy_sphere(level=4, seed=1),
+        "table": M.table(4),
+        "box": M.box(0.7, 0.5, 0.3, 1),
+        "holes": M.bumpy_sphere(level=4, seed=2, decimate_to=3000),
+    }
+
+
+def compare(rac_out, orc, W, H, tag=""):
+    rgb_o, depth_o, rgba_o = orc
+    depth = rac_out["depth"].cpu().numpy()
+    npx = depth[0].size
+    cov, cov_o = depth > 0, depth_o > 0
+    mism = (cov != cov_o).reshape(len(depth), -1).sum(1)
+    assert (mism <= 0.001 * npx).all(), f"{tag} coverage mismatch pixels per image: {mism}"
+    both = cov & cov_o
+    rel = np.abs(depth - depth_o)[both] / depth_o[both]
+    bad = (rel > 1e-5).sum()
+    assert bad <= 0.001 * both.sum() + 1, f"{tag} depth: {bad} of {both.sum()} pixels off by > 1e-5 rel (max {rel.max()})"
+    if rac_out.get("rgba8") is not None:
+        q = rac_out["rgba8"].cpu().numpy().astype(np.int32)
+        dq = np.abs(q[..., :3] - rgba_o[..., :3].astype(np.int32)).max(-1)
+        assert ((dq > 2).reshape(len(depth), -1).sum(1) <= 0.001 * npx).all(), f"{tag} rgba8 off by > 2 LSB: {(dq > 2).sum()}"
+    if rac_out.get("rgb") is not None:
+        rgb = rac_out["rgb"].cpu().numpy()
+        d = np.abs(rgb - rgb_o).max(-1)
+        nbad = (d > 2.0 / 255.0).reshape(len(depth), -1).sum(1)
+        assert (nbad <= 0.001 * npx).all(), f"{tag} colour off by > 2/255 on {nbad} pixels (max {d.max()})"
+    return mism
+
+
+@pytest.mark.parametrize("name", ["ico3", "bumpy5k", "table", "box", "holes"])
+def test_render_matches_oracle(rac, name):
+    m = meshes()[name]
+    B, W, H = 6, 320, 320
+    T, _ = sample_poses(B, seed=sum(map(ord, name)))
+    K = intrinsics(B, W, H)
+    out = rac.render_batch_device(T, m, K, W, want_rgba8=True)
+    compare(out, ro.render_batch(m, T, K, W), W, H, name)
+    d = out["depth"].cpu().numpy()
+    assert (d > 0).mean() > 0.02, "object should be visible"
+    rgb = out["rgb"].cpu().numpy()
+    assert rgb.max() == pytest.approx(1.0) and rgb.min() >= 0.0          # R9 max-normalisation
+
+
+@pytest.mark.parametrize("W,H", [(320, 240), (224, 224), (300, 300), (101, 67), (640, 480)])
+def test_render_resolutions(rac, W, H):
+    m = meshes()["bumpy5k"]
+    B = 3
+    T, _ = sample_poses(B, seed=W + H)
+    K = intrinsics(B, W, H)
+    out = rac.render_batch_device(T, m, K, (W, H), want_rgba8=True)
+    assert out["rgb"].shape == (B, H, W, 3) and out["depth"].shape == (B, H, W)
+    compare(out, ro.render_batch(m, T, K, (W, H)), W, H, f"{W}x{H}")
+
+
+def test_bit_exact_depth_and_coverage_on_most_images(rac):
+    """The coverage/depth spec is op-by-op deterministic; CPU and GPU should agree bit for bit."""
+    m = meshes()["bumpy5k"]
+    B, S = 8, 320
+    T, _ = sample_poses(B, seed=77)
+    K = intrinsics(B, S, S)
+    out = rac.render_batch_device(T, m, K, S)
+    _, depth_o, _ = ro.render_batch(m, T, K, S)
+    depth = out["depth"].cpu().numpy()
+    exact = [(depth[i] == depth_o[i]).all() for i in range(B)]
+    assert sum(exact) >= B - 1, exact
+
+
+def test_mixed_meshes_and_vertex_colours(rac):
+    from rac import mesh as M
+    ms = meshes()
+    vc = M.icosphere(3)
+    rng = np.random.default_rng(0)
+    vc.vcolor = np.concatenate([rng.integers(30, 255, size=(len(vc.verts), 3)), np.full((len(vc.verts), 1), 255)], 1).astype(np.uint8)
+    batch = [ms["table"], vc, ms["bumpy5k"], ms["table"], vc, ms["box"]]
+    B, S = len(batch), 256
+    T, _ = sample_poses(B, seed=5)
+    K = intrinsics(B, S, S)
+    out = rac.render_batch_device(T, batch, K, S, want_rgba8=True)
+    compare(out, ro.render_batch_mixed(batch, T, K, S), S, S, "mixed")
+    q = out["rgba8"][1].cpu().numpy()
+    assert (q[..., 0].astype(int) != q[..., 1].astype(int)).any(), "vertex colours must tint the render"
+
+
+def test_textured_mesh(rac):
+    from rac import mesh as M
+    m = M.with_texture(M.icosphere(4), size=128, seed=3)
+    B, S = 4, 320
+    T, _ = sample_poses(B, seed=9)
+    K = intrinsics(B, S, S)
+    out = rac.render_batch_device(T, m, K, S, want_rgba8=True)
+    compare(out, ro.render_batch(m, T, K, S), S, S, "textured")
+
+
+def test_edge_cases(rac):
+    m = meshes()["box"]
+    S = 128
+    K = intrinsics(4, S, S)
+    T = np.tile(np.eye(4, dtype=np.float32), (4, 1, 1))
+    T[0, 2, 3] = 2.5                      # visible
+    T[1, 2, 3] = -2.5                     # behind the camera -> empty
+    T[2, 2, 3] = 2.5; T[2, 0, 3] = 50.0   # far off-screen -> empty
+    T[3, 2, 3] = 0.2                      # straddles the near plane: triangles with a vertex < znear are dropped
+    out = rac.render_batch_device(T, m, K, S, want_rgba8=True)
+    orc = ro.render_batch(m, T, K, S)
+    compare(out, orc, S, S, "edge")
+    d = out["depth"].cpu().numpy()
+    assert (d[0] > 0).any() and not (d[1] > 0).any() and not (d[2] > 0).any()
+    rgb = out["rgb"].cpu().numpy()
+    assert rgb[1].max() == 0.0 and np.isfinite(rgb).all()     # renderer.py:103: no division when max == 0
+    # fronto-parallel face: constant depth = distance to the near face (box half depth 0.15)
+    centre = d[0][S // 2 - 4:S // 2 + 4, S // 2 - 4:S // 2 + 4]
+    np.testing.assert_allclose(centre, 2.5 - 0.15, rtol=2e-5)
+
+
+@pytest.mark.parametrize("use_depth", [False, True])
+@pytest.mark.parametrize("W,H", [(320, 240), (99, 65)])
+def test_render_concat_matches_oracle_pipeline(rac, use_depth, W, H):
+    """render + prepare_model_input fused (rac_render_concat) == oracle render -> numpy restatement
+    of prepare_model_input (data_loaders.py:158-177)."""
+    m = meshes()["bumpy5k"]
+    B = 5
+    T_init, T_gt = sample_poses(B, seed=21)
+    K = intrinsics(B, W, H)
+    rng = np.random.default_rng(1)
+    gt_rgb, _, _ = ro.render_batch(m, T_gt, K, (W, H))
+    gt = np.clip(gt_rgb * 255 + rng.uniform(0, 8, gt_rgb.shape), 0, 255).astype(np.uint8).astype(np.float64) / 255.0
+    x, depth, rgb = rac.render_concat_device(T_init, m, K, (W, H), gt.astype(np.float32), use_norm_depth=use_depth,
+                                             want_depth=True, want_rgb=True)
+    rgb_o, depth_o, _ = ro.render_batch(m, T_init, K, (W, H))
+    ref = assemble_ref.prepare_model_input(rgb_o, gt, depth_o, use_depth).numpy()
+    x = x.cpu().numpy()
+    assert x.shape == ref.shape == (B, 7 if use_depth else 6, H, W)
+    npx = W * H
+    c0 = 1 if use_depth else 0
+    # render channels: colour tolerance 2/255 except <= 0.1% edge pixels
+    bad = (np.abs(x[:, c0:c0 + 3] - ref[:, c0:c0 + 3]).max(1) > 2 / 255).reshape(B, -1).sum(1)
+    assert (bad <= 0.001 * npx).all(), bad
+    # gt channels: pure arithmetic, 1e-5 with an absolute floor
+    np.testing.assert_allclose(x[:, c0 + 3:], ref[:, c0 + 3:], rtol=1e-5, atol=2e-6)
+    if use_depth:
+        dd = np.abs(x[:, 0] - ref[:, 0])
+        bad = (dd > 1e-5 * np.abs(ref[:, 0]) + 2e-5).reshape(B, -1).sum(1)
+        assert (bad <= 0.001 * npx).all(), (bad, dd.max())
+    np.testing.assert_allclose(rgb.cpu().numpy().transpose(0, 3, 1, 2), x[:, c0:c0 + 3], rtol=0, atol=0)
+
+
+@pytest.mark.parametrize("use_depth", [False, True])
+def test_assemble_input_only(rac, use_depth):
+    """prepare_model_input on existing renders (iteration 0 path), incl. the Q10 early returns."""
+    rng = np.random.default_rng(2)
+    B, H, W = 4, 60, 80
+    init = rng.uniform(0, 1, (B, H, W, 3)).astype(np.float32)
+    gt = (rng.integers(0, 256, (B, H, W, 3)) / 255.0)
+    depth = np.where(rng.uniform(size=(B, H, W)) > 0.6, rng.uniform(2.2, 2.8, (B, H, W)), 0).astype(np.float32)
+    depth[1] = 0.0                      # max <= 0.1 -> returned unchanged
+    depth[2] = np.where(depth[2] > 0, 2.5, 0).astype(np.float32)   # std == 0 -> returned unchanged
+    x = rac.assemble_input_device(init, gt.astype(np.float32), depth, use_depth).cpu().numpy()
+    ref = assemble_ref.prepare_model_input(init, gt, depth, use_depth).numpy()
+    np.testing.assert_allclose(x, ref, rtol=1e-5, atol=2e-5)
+    c = ro.prepare_model_input_c(init, gt.astype(np.float32), depth, use_depth)
+    np.testing.assert_allclose(c, ref, rtol=1e-5, atol=2e-5)
+
+
+def test_reference_api_modules(rac, tmp_path):
+    """The drop-in modules: renderer.render_scene, data_loaders.render_batch / prepare_model_input."""
+    import data_loaders
+    import renderer
+    from rac import mesh as M
+    m = meshes()["table"]
+    path = str(tmp_path / "table.ply")
+    M.save_ply(path, m)
+    S = 160
+    T, Tg = sample_poses(3, seed=3)
+    Kc = renderer.get_camera_matrix({"focal_length": 50, "sensor_width": 36, "image_resolution": S})
+    img, depth = renderer.render_scene(path, T[0], K=Kc, img_size=S)
+    assert img.shape == (S, S, 3) and img.dtype == np.float64 and depth.shape == (S, S) and depth.dtype == np.float32
+    rgb_o, depth_o, _ = ro.render_batch(M.load_ply(path), T[:1], Kc[None].astype(np.float32), S)
+    assert (np.abs(img - rgb_o[0]).max(-1) > 2 / 255).sum() <= 0.001 * S * S
+    Ks = torch.tensor(np.tile(Kc, (3, 1, 1)))             # train_model.py:240 passes a torch tensor
+    imgs, depths = data_loaders.render_batch(T, [path] * 3, Ks, S)
+    assert imgs.shape == (3, S, S, 3) and np.asarray(imgs).dtype == np.float32 and np.asarray(depths).shape == (3, S, S)
+    np.testing.assert_array_equal(np.asarray(imgs)[0], img.astype(np.float32))
+    gt = np.asarray(imgs)[::-1].copy().astype(np.float64)
+    x = data_loaders.prepare_model_input(imgs, gt, depths, use_norm_depth=True)
+    ref = assemble_ref.prepare_model_input(np.asarray(imgs), gt, np.asarray(depths), True)
+    assert x.shape == (3, 7, S, S) and x.dtype == torch.float32
+    np.testing.assert_allclose(x.cpu().numpy(), ref.numpy(), rtol=1e-5, atol=2e-5)
+    np.testing.assert_allclose(data_loaders.normalize_img(gt[0]), assemble_ref.normalize_img(gt[0]), rtol=1e-5, atol=2e-6)
+    np.testing.assert_allclose(data_loaders.normalize_depth(np.asarray(depths)[0]),
+                               assemble_ref.normalize_depth(np.asarray(depths)[0]), rtol=1e-5, atol=2e-5)
+    with pytest.raises(AssertionError):
+        data_loaders.render_batch_sequential(T[:2], [path] * 3, Ks, S)
+
+
+def test_full_size_properties(rac):
+    """BASELINE config size (B=64, 320x240, ~10k triangles): size-independent properties —
+    determinism, batch-permutation equivariance, and sub-batch consistency."""
+    from rac import mesh as M
+    m = M.bumpy_sphere(level=5, seed=3, decimate_to=10000)
+    B, W, H = 64, 320, 240
+    T, Tg = sample_poses(B, seed=11)
+    K = intrinsics(B, W, H)
+    a = rac.render_batch_device(T, m, K, (W, H), want_rgba8=True)
+    b = rac.render_batch_device(T, m, K, (W, H), want_rgba8=True)
+    assert torch.equal(a["rgba8"], b["rgba8"]) and torch.equal(a["depth"], b["depth"]) and torch.equal(a["rgb"], b["rgb"])
+    perm = np.random.default_rng(0).permutation(B)
+    c = rac.render_batch_device(T[perm], m, K, (W, H), want_rgba8=True)
+    assert torch.equal(c["rgba8"], a["rgba8"][perm]) and torch.equal(c["depth"], a["depth"][perm])
+    d = rac.render_batch_device(T[:7], m, K[:7], (W, H), want_rgba8=True)
+    assert torch.equal(d["rgba8"], a["rgba8"][:7]) and torch.equal(d["rgb"], a["rgb"][:7])
+    # and a sample of the big batch against the oracle
+    idx = [0, 13, 63]
+    compare({k: v[idx] for k, v in a.items()}, ro.render_batch(m, T[idx], K[idx], (W, H)), W, H, "full")
+    # projected mesh vertices that are visible must land on covered pixels (SURVEY 8c self-check)
+    depth = a["depth"][0].cpu().numpy()
+    P = (T[0, :3, :3] @ m.verts.T).T + T[0, :3, 3]
+    u = np.floor(K[0, 0, 0] * P[:, 0] / P[:, 2] + K[0, 0, 2]).astype(int)
+    v = np.floor(K[0, 1, 1] * P[:, 1] / P[:, 2] + K[0, 1, 2]).astype(int)
+    ok = (u >= 1) & (u < W - 1) & (v >= 1) & (v < H - 1)
+    dz = depth[v[ok], u[ok]]
+    front = np.abs(dz - P[ok, 2]) < 0.01
+    assert front.mean() > 0.25 and (dz[front] > 0).all()
