@@ -1,0 +1,383 @@
+#!/usr/bin/env python
+"""bench.py — render-and-compare hot path on N B200s (one process per GPU).
+
+One *step* = one refinement iteration of the reference's inner loop for one batch
+(train_model.py:240-250 with the stock CNN taken out):
+    render under T_CO_pred + normalise + concat with the gt crop  -> x (B,6,H,W)      [rac_render_concat]
+    head output y (synthetic, resident)  -> calculate_T_CO_pred('6D')               [rac_pose_update_fwd]
+    compute_disentangled_ADD_L1_loss(T_gt, T_new, verts) + backward to y             [rac_add_loss_fwd/bwd, rac_pose_update_bwd]
+Workload (BASELINE.json configs[1], at the shape its `metric` names): batch 64 per GPU, 320x240,
+one synthetic ModelNet10-scale untextured mesh of ~10k triangles, 6D head, N=1000 loss points.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+For N>1 launch with torch.distributed.run (the driver does); weak scaling: every rank renders its own
+64 poses, the only collective is the scalar loss all-reduce (NCCL).
+
+`value`   = renders/s with inputs resident in HBM (device-timed, CUDA events on the launching stream).
+`e2e`     = the same through the reference-facing Python API (data_loaders.render_batch /
+            prepare_model_input / calculate_T_CO_pred / loss) with HOST (pinned) buffers in, host pose out.
+`roofline`= the rasterize+concat stage (setup + raster + finalize kernels of one rac_render_concat call),
+            algorithmic bytes 36*W*H per image over its CUDA-event time.
+`--impl reference` times the CPU oracle (oracle/: C rasteriser restatement + reference-restated torch CPU
+pose/loss) on the host cores — the reference's own renderer needs OpenGL and is unavailable on this box.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "end-to-end-rgb-pose-estimation-baseline_b200")
+for _p in (PKG, ROOT):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+METRIC = "render-and-compare renders/sec (bs 64 per GPU, 320x240)"
+UNIT = "renders/s"
+B, W, H, NPTS, NTRI = 64, 320, 240, 1000, 10000
+NSETS = 4            # rotating input/output sets: 4 x (59 MB gt + 118 MB x) >> 126 MB L2
+ROT, LOSS = "6D", "add_l1_disentangled"
+
+
+def workload_name():
+    return ("effnet_b3_6d-shape hot path: B=%d/GPU, %dx%d, untextured %d-tri mesh, 6D head, "
+            "disentangled ADD-L1 (N=%d), CNN excluded (stock PyTorch, not on the path)" % (B, W, H, NTRI, NPTS))
+
+
+def make_inputs(seed):
+    """Synthetic inputs per SURVEY.md §8d: poses drawn like se3_helpers.get_T_CO_init_and_gt."""
+    from rac import mesh as M
+    import se3_helpers
+    mesh = M.bumpy_sphere(level=5, seed=1, decimate_to=NTRI)
+    scene_cfg = dict(distance_cam_to_world=2.5, distance_cam_to_world_deviation=0.1,
+                     world_to_object_gt_transl_deviation=0.1, world_to_object_transl_deviation=0.1,
+                     world_to_object_angle_deviation=30)
+    rng = np.random.default_rng(seed)
+    np.random.seed(seed)
+    sets = []
+    for _ in range(NSETS):
+        ti, tg = [], []
+        for _ in range(B):
+            a, b = se3_helpers.get_T_CO_init_and_gt(scene_cfg)
+            ti.append(a.data[0]); tg.append(b.data[0])
+        T_init, T_gt = np.array(ti, np.float32), np.array(tg, np.float32)
+        y = (0.1 * rng.normal(size=(B, 9))).astype(np.float32)
+        y[:, 0] += 1.0; y[:, 4] += 1.0                       # near-identity 6D columns
+        y[:, 6:8] *= 0.2; y[:, 8] = 1.0 + 0.05 * rng.normal(size=B)   # vx, vy small; vz ~ 1 (Q4)
+        pts = mesh.verts[rng.integers(0, len(mesh.verts), (B, NPTS))].astype(np.float32)
+        sets.append(dict(T_init=T_init, T_gt=T_gt, y=y, pts=pts))
+    fx = 50.0 / (36.0 / W)
+    K = np.tile(np.array([[fx, 0, W / 2.0], [0, fx, H / 2.0], [0, 0, 1]], np.float32), (B, 1, 1))
+    return mesh, sets, K
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock + throttle reasons through NVML during the timed region."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.stop_flag, self.sm, self.reasons, self.sm_max = index, False, [], set(), None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {getattr(nv, k): v for k, v in (
+            ("nvmlClocksEventReasonHwSlowdown", "hw_slowdown"),
+            ("nvmlClocksEventReasonHwThermalSlowdown", "hw_thermal_slowdown"),
+            ("nvmlClocksEventReasonSwThermalSlowdown", "sw_thermal_slowdown"),
+            ("nvmlClocksEventReasonSwPowerCap", "sw_power_cap"),
+            ("nvmlClocksEventReasonHwPowerBrakeSlowdown", "hw_power_brake")) if hasattr(nv, k)}
+        while not self.stop_flag:
+            try:
+                self.sm.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, nm in names.items():
+                    if r & bit:
+                        self.reasons.add(nm)
+            except Exception:
+                pass
+            time.sleep(0.02)
+
+    def result(self):
+        self.stop_flag = True
+        if self.nv is None or not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": [], "note": "nvml unavailable"}
+        return {"sm_mhz": float(np.median(self.sm)), "sm_max_mhz": self.sm_max, "reasons": sorted(self.reasons),
+                "samples": len(self.sm)}
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    import rac
+    import data_loaders as DL
+    import loss as L
+    import rotation_representation as RR
+    from rac import mesh as M
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — the render-and-compare path is CUDA-only (no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    rac.lib()
+
+    mesh, sets, K = make_inputs(seed=1000 + rank)
+    ply = "/tmp/rac_bench_mesh_r%d.ply" % rank
+    M.save_ply(ply, mesh)
+    mesh_paths = [ply] * B
+    Ks_cpu = torch.tensor(K)                      # stays on the CPU like the reference's cam_mats (Q5)
+    Kd = Ks_cpu.to(dev)
+
+    # gt crops: our own render at T_gt + U(0,8)/255 noise, quantised to u8
+    g = torch.Generator(device=dev); g.manual_seed(7 + rank)
+    dsets = []
+    for s in sets:
+        r = rac.render_batch_device(s["T_gt"], ply, K, (W, H), want_depth=False)["rgb"]
+        gt = torch.clamp(torch.round(r * 247.0 + torch.rand(r.shape, device=dev, generator=g) * 8.0), 0, 255) / 255.0
+        d = dict(T_init=torch.tensor(s["T_init"], device=dev), T_gt=torch.tensor(s["T_gt"], device=dev),
+                 y=torch.tensor(s["y"], device=dev).requires_grad_(True), pts=torch.tensor(s["pts"], device=dev),
+                 gt=gt.contiguous(), x=torch.empty((B, 6, H, W), dtype=torch.float32, device=dev))
+        # pinned host copies for the e2e arm
+        d["h_gt"] = gt.cpu().pin_memory()
+        d["h_T_init"] = torch.tensor(s["T_init"]).pin_memory()
+        d["h_T_gt"] = torch.tensor(s["T_gt"]).pin_memory()
+        d["h_y"] = torch.tensor(s["y"]).pin_memory()
+        d["h_pts"] = torch.tensor(s["pts"]).pin_memory()
+        dsets.append(d)
+    loss_buf = torch.zeros(1, device=dev)
+
+    def step_device(i, ev=None):
+        s = dsets[i % NSETS]
+        if ev is not None:
+            ev[0].record()
+        rac.render_concat_device(s["T_init"], ply, Kd, (W, H), s["gt"], use_norm_depth=False, out=s["x"])
+        if ev is not None:
+            ev[1].record()
+        s["y"].grad = None
+        T_new = RR.calculate_T_CO_pred(s["y"], s["T_init"], ROT, Ks_cpu)
+        l = L.compute_disentangled_ADD_L1_loss(s["T_gt"], T_new, s["pts"])     # train_model.py:280 argument order
+        l.backward()
+        loss_buf.copy_(l.detach().reshape(1))
+        if world > 1:
+            dist.all_reduce(loss_buf)              # the logged loss mean
+        return T_new
+
+    h_pose_out = torch.empty((B, 4, 4), dtype=torch.float32).pin_memory()
+    h_loss_out = torch.empty(1, dtype=torch.float32).pin_memory()
+
+    def step_e2e(i):
+        """The reference-facing calls of train_model.py:240-250 on HOST buffers."""
+        s = dsets[i % NSETS]
+        T_pred = s["h_T_init"].numpy()
+        imgs, depths = DL.render_batch_sequential(T_pred, mesh_paths, Ks_cpu, (W, H))          # :240
+        T_dev = s["h_T_init"].to(dev, non_blocking=True)                                       # :241
+        x = DL.prepare_model_input(imgs, s["h_gt"], depths, False).to(dev)                     # :243
+        y = s["h_y"].to(dev, non_blocking=True).requires_grad_(True)                           # (CNN output stand-in)
+        T_gt = s["h_T_gt"].to(dev, non_blocking=True)
+        pts = s["h_pts"].to(dev, non_blocking=True)
+        T_new = RR.calculate_T_CO_pred(y, T_dev, ROT, Ks_cpu)                                  # :245
+        l = L.compute_disentangled_ADD_L1_loss(T_gt, T_new, pts)                               # :247 / :280
+        l.backward()
+        if world > 1:
+            lb = l.detach().reshape(1).clone()
+            dist.all_reduce(lb)
+        h_pose_out.copy_(T_new.detach(), non_blocking=True)                                    # :250
+        h_loss_out.copy_(l.detach().reshape(1), non_blocking=True)                             # :254 (.item())
+        torch.cuda.current_stream().synchronize()
+        return x
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, with_stage_events):
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)] \
+            if with_stage_events else None
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        w0 = time.perf_counter()
+        t0.record()
+        for i in range(steps):
+            if evs is not None:
+                fn(i, evs[i])
+            else:
+                fn(i)
+        t1.record()
+        barrier()
+        wall = (time.perf_counter() - w0) * 1e3
+        ms = t0.elapsed_time(t1)
+        stage = float(np.mean([a.elapsed_time(b) for a, b in evs])) if evs else None
+        tt = torch.tensor([ms, wall], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        return float(tt[0]), float(tt[1]), stage
+
+    for i in range(max(args.warmup, 3)):
+        step_device(i)
+    n0 = rac.launch_count()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms, wall_ms, stage_ms = timed(step_device, args.steps, True)
+    launches = rac.launch_count() - n0
+    clocks = sampler.result()
+
+    for i in range(max(args.warmup, 3)):
+        step_e2e(i)
+    e_ms, e_wall_ms, _ = timed(step_e2e, args.steps, False)
+    e_ms = max(e_ms, e_wall_ms)      # e2e includes host work: take the larger of device and wall clocks
+
+    per_step = ms / args.steps
+    value = world * B * args.steps / (ms * 1e-3)
+    algo_bytes = 36.0 * W * H * B + (12.0 * len(mesh.verts) + 12.0 * len(mesh.faces)) + 100.0 * B
+    peaks = {}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            peaks = json.load(f)
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = algo_bytes / (stage_ms * 1e-3) / 1e9
+    h2d = sum(dsets[0][k].numel() * 4 for k in ("h_gt", "h_T_init", "h_T_gt", "h_y", "h_pts"))
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "iters_per_sec": world * args.steps / (ms * 1e-3),
+        "config": {"workload": workload_name(), "global_batch": world * B, "width": W, "height": H, "triangles": len(mesh.faces),
+                   "rot_repr": ROT, "loss": LOSS, "points": NPTS, "parallelism": "dp%d (batch sharded, no data-path collective)" % world,
+                   "l2": "rotating %d input/output sets (%.0f MB each) > 126 MB L2" % (NSETS, (36.0 * W * H * B) / 1e6)},
+        "roofline": {"bound": "hbm", "kernel": "rac_render_concat stage (setup_kernel + raster_kernel + finalize_concat_kernel)",
+                     "achieved": achieved, "peak": peak, "peak_source": "measured" if peaks else "fallback",
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "stage_ms": stage_ms, "algorithmic_bytes": algo_bytes,
+                     "triangle_setup_rate_per_s": B * len(mesh.faces) / (stage_ms * 1e-3)},
+        "e2e": {"value": world * B * args.steps / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms / args.steps,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 64 + 4,
+                "api": "data_loaders.render_batch_sequential + prepare_model_input + calculate_T_CO_pred + compute_disentangled_ADD_L1_loss + backward"},
+        "gpu_launches": int(launches), "clocks": clocks,
+    }
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(seconds=15.0)
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------------------------------------
+# CPU baseline / reference arm: the oracle (CPU restatement) timed on the host cores
+# ---------------------------------------------------------------------------------------------
+def _cpu_step_factory(nb):
+    """One CPU pass of the same hot path over `nb` poses of the bench workload (oracle/ code only)."""
+    import torch
+    from oracle import pose_loss_ref, raster_oracle
+    mesh, sets, K = make_inputs(seed=1000)
+    s = sets[0]
+    cores = raster_oracle.num_threads()
+    torch.set_num_threads(cores)
+    T = s["T_init"][:nb]
+    Kb = K[:nb]
+    gt, _, _ = raster_oracle.render_batch(mesh, s["T_gt"][:nb], Kb, (W, H), want_rgba8=False)
+    y0 = torch.tensor(s["y"][:nb])
+    T_gt = torch.tensor(s["T_gt"][:nb])
+    pts = torch.tensor(s["pts"][:nb])
+    Ks = torch.tensor(Kb)
+
+    def step():
+        rgb, depth, _ = raster_oracle.render_batch(mesh, T, Kb, (W, H), want_rgba8=False)     # renderer.py:85-105 x nb
+        x = raster_oracle.prepare_model_input_c(rgb, gt, depth, False)                        # data_loaders.py:158-177
+        y = y0.clone().requires_grad_(True)
+        T_new = pose_loss_ref.pose_update(y, torch.tensor(T), ROT, Ks)                        # rotation_representation.py:131-184
+        l = pose_loss_ref.disentangled(T_gt, T_new, pts)                                      # loss.py:81-97 (train_model.py:280 order)
+        l.backward()
+        return x, float(l.detach())
+
+    return step, cores
+
+
+def cpu_baseline(seconds=15.0, nb=B):
+    step, cores = _cpu_step_factory(nb)
+    step()
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        step()
+        n += 1
+        dt = time.perf_counter() - t0
+        if dt > seconds or n >= 200:
+            break
+    return {"value": nb * n / dt, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": "%d passes of %d poses (of the B=%d workload) through oracle/raster_ref.c (OpenMP, %d threads) + "
+                      "oracle prepare_model_input + oracle/pose_loss_ref.py fwd+bwd; %.1f s" % (n, nb, B, cores, dt)}
+
+
+def run_reference(args):
+    """--impl reference: the reference's path on the host cores.  The reference's renderer is pyrender/OpenGL
+    (unavailable on this box, no CPU path of its own), so this arm is the oracle port, all host threads."""
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if rank != 0:
+        return
+    nb = B
+    step, cores = _cpu_step_factory(nb)
+    for _ in range(max(args.warmup, 1)):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = time.perf_counter() - t0
+    v = nb * args.steps / dt
+    sample = "%d timed steps, each %d poses of the B=%d workload (bounded sample), %d host threads" % (args.steps, nb, B, cores)
+    out = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+           "warmup": max(args.warmup, 1), "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": workload_name(), "global_batch": nb, "width": W, "height": H, "triangles": NTRI,
+                      "rot_repr": ROT, "loss": LOSS, "points": NPTS,
+                      "note": "reference renderer = pyrender/OpenGL: unavailable on this box; CPU oracle port timed instead"},
+           "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+           "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~15 s CPU oracle leg (profiling runs)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()
