@@ -4,763 +4,61 @@
 // pyrender/OpenGL (R1-R9 in SURVEY.md §8a), and data_loaders.py:158-177 (prepare_model_input).
 //
 // Three kernels per call (see raster.cuh for the spec they implement):
-//   setup_kernel     one thread per (image, triangle): transform, project, snap, cull, 1/z plane,
-//                    camera-frame normal -> TriRec; survivors appended to a per-image list.
-//   raster_kernel    one CTA per (image, band of rows): the band's 4x-MSAA visibility buffer
-//                    (depth24 | triangle id, 8 B per sample) lives in shared memory; triangles
-//                    are scattered into it with shared-memory atomic-min, then every pixel is
-//                    shaded + resolved once and written as RGBA8 + f32 depth; per-image
-//                    max / mean / std accumulators are reduced per CTA and flushed with atomics.
-//   finalize_*       streaming pass: RGBA8+depth (L2-resident) [+ gt crop] -> normalised f32
-//                    outputs with 128-bit coalesced stores (NCHW concat or HWC render).
+//   setup_kernel     (raster_setup.inl) one thread per (image, triangle): transform, project, snap, cull,
+//                    1/z plane, camera-frame normal -> TriRec.  The CTA (256 triangles of one image) bins
+//                    its survivors by 32x32-px tile in shared memory and publishes, without any global
+//                    atomic, a private ref region (u8 local ids grouped by tile) plus one descriptor per
+//                    tile.  Triangles spanning more than 2x2 tiles go to a per-image large list.
+//   raster_kernel    (raster_tile.inl, raster_shade.inl) one CTA per (image, tile): the tile's 4x-MSAA
+//                    visibility buffer (depth24 | triangle id, 8 B per sample, 32 KB) lives in shared
+//                    memory; the tile's triangles are gathered through the descriptors and scattered into
+//                    it with shared-memory atomic-min (exact int32 edge functions for binned triangles,
+//                    int64 for large ones); then every pixel is shaded + resolved once and written as
+//                    RGBA8 + f32 depth; per-image max / mean / std accumulators are reduced per CTA and
+//                    flushed with atomics.
+//   finalize_*       (raster_finalize.inl) streaming pass: RGBA8+depth (L2-resident) [+ gt crop] ->
+//                    normalised f32 outputs with 128-bit coalesced stores (NCHW concat or HWC render).
 #include "raster.cuh"
 #include <mutex>
 #include <math.h>
 
 namespace rac {
 
-// ---------------------------------------------------------------------------------------------
-// setup
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ int floor_div256(int a) { return a >> 8; }             // arithmetic shift
-__device__ __forceinline__ int ceil_div256(int a) { return (a + 255) >> 8; }
-
-struct CamPose {
-    float r[9];
-    float t[3];
-    float fx, fy, cx, cy;
-};
-
-__device__ __forceinline__ CamPose load_campose(const float* __restrict__ T_CO, const float* __restrict__ K, int b) {
-    CamPose c;
-    const float* T = T_CO + 16 * (size_t)b;
-    c.r[0] = T[0]; c.r[1] = T[1]; c.r[2] = T[2];  c.t[0] = T[3];
-    c.r[3] = T[4]; c.r[4] = T[5]; c.r[5] = T[6];  c.t[1] = T[7];
-    c.r[6] = T[8]; c.r[7] = T[9]; c.r[8] = T[10]; c.t[2] = T[11];
-    const float* k = K + 9 * (size_t)b;
-    c.fx = k[0]; c.cx = k[2]; c.fy = k[4]; c.cy = k[5];   // ref: renderer.py:72 (fx, fy, ux, uy only)
-    return c;
-}
-
-// RS-V. Returns false when the vertex invalidates its triangle.
-__device__ __forceinline__ bool project_vertex(const CamPose& c, const float* __restrict__ p, float znear,
-                                               int& X, int& Y, float& iz) {
-    const float px = p[0], py = p[1], pz = p[2];
-    const float xc = __fmaf_rn(c.r[2], pz, __fmaf_rn(c.r[1], py, __fmaf_rn(c.r[0], px, c.t[0])));
-    const float yc = __fmaf_rn(c.r[5], pz, __fmaf_rn(c.r[4], py, __fmaf_rn(c.r[3], px, c.t[1])));
-    const float zc = __fmaf_rn(c.r[8], pz, __fmaf_rn(c.r[7], py, __fmaf_rn(c.r[6], px, c.t[2])));
-    if (!(zc >= znear)) return false;
-    iz = __fdiv_rn(1.0f, zc);
-    const float u = __fmaf_rn(c.fx, __fmul_rn(xc, iz), c.cx);
-    const float v = __fmaf_rn(c.fy, __fmul_rn(yc, iz), c.cy);
-    if (!(fabsf(u) <= kGuardPx) || !(fabsf(v) <= kGuardPx)) return false;
-    X = __float2int_rn(__fmul_rn(u, (float)kSubpix));
-    Y = __float2int_rn(__fmul_rn(v, (float)kSubpix));
-    return true;
-}
-
-__global__ void __launch_bounds__(256)
-setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
-             const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT,
-             float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ surv_y,
-             unsigned* __restrict__ surv_tri, int4* __restrict__ recs) {
-    const int b = blockIdx.y;
-    const MeshDev& mesh = table[mesh_ids ? mesh_ids[b] : uniform_mesh];
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    const int T = mesh.T;
-    if (blockIdx.x * blockDim.x >= T) return;   // whole CTA beyond this image's mesh
-    const CamPose cam = load_campose(T_CO, K, b);
-
-    bool keep = t < T;
-    int X0 = 0, Y0 = 0, X1 = 0, Y1 = 0, X2 = 0, Y2 = 0;
-    float iz0 = 0.f, iz1 = 0.f, iz2 = 0.f;
-    unsigned ypack = 0;
-    if (keep) {
-        const int i0 = mesh.faces[3 * t], i1 = mesh.faces[3 * t + 1], i2 = mesh.faces[3 * t + 2];
-        keep = project_vertex(cam, mesh.verts + 3 * (size_t)i0, znear, X0, Y0, iz0);
-        keep = keep && project_vertex(cam, mesh.verts + 3 * (size_t)i1, znear, X1, Y1, iz1);
-        keep = keep && project_vertex(cam, mesh.verts + 3 * (size_t)i2, znear, X2, Y2, iz2);
-    }
-    long long area2 = 0;
-    if (keep) {
-        area2 = (long long)(X1 - X0) * (Y2 - Y0) - (long long)(X2 - X0) * (Y1 - Y0);
-        keep = area2 < 0;   // RS-T: front faces have negative area in (u, v-down) image coordinates
-    }
-    if (keep) {
-        // pixels that own at least one sample inside the bounding box (sample offsets span 32..224)
-        const int xmin = min(X0, min(X1, X2)), xmax = max(X0, max(X1, X2));
-        const int ymin = min(Y0, min(Y1, Y2)), ymax = max(Y0, max(Y1, Y2));
-        const int px0 = max(ceil_div256(xmin - 224), 0), px1 = min(floor_div256(xmax - 32), W - 1);
-        const int py0 = max(ceil_div256(ymin - 224), 0), py1 = min(floor_div256(ymax - 32), H - 1);
-        keep = (px0 <= px1) && (py0 <= py1);
-        ypack = (unsigned)py0 | ((unsigned)py1 << 16);
-    }
-    if (keep) {
-        // swap v1 <-> v2 so that the interior is on the non-negative side of all three edges
-        int tx = X1, ty = Y1; X1 = X2; Y1 = Y2; X2 = tx; Y2 = ty;
-        float tz = iz1; iz1 = iz2; iz2 = tz;
-        const float areaf = (float)(-area2);
-        const float d1 = __fsub_rn(iz1, iz0), d2 = __fsub_rn(iz2, iz0);
-        const float ex1 = (float)(X1 - X0), ey1 = (float)(Y1 - Y0);
-        const float ex2 = (float)(X2 - X0), ey2 = (float)(Y2 - Y0);
-        const float gx = __fdiv_rn(__fmaf_rn(d1, ey2, -__fmul_rn(d2, ey1)), areaf);
-        const float gy = __fdiv_rn(__fmaf_rn(d2, ex1, -__fmul_rn(d1, ex2)), areaf);
-        const float* fn = mesh.fnormals + 3 * (size_t)t;
-        const float nx = cam.r[0] * fn[0] + cam.r[1] * fn[1] + cam.r[2] * fn[2];
-        const float ny = cam.r[3] * fn[0] + cam.r[4] * fn[1] + cam.r[5] * fn[2];
-        const float nz = cam.r[6] * fn[0] + cam.r[7] * fn[1] + cam.r[8] * fn[2];
-        int4* r = recs + 3 * ((size_t)b * maxT + t);
-        r[0] = make_int4(X0, Y0, X1, Y1);
-        r[1] = make_int4(X2, Y2, __float_as_int(iz0), __float_as_int(gx));
-        r[2] = make_int4(__float_as_int(gy), __float_as_int(nx), __float_as_int(ny), __float_as_int(nz));
-    }
-    // warp-aggregated append to the image's survivor list
-    const unsigned m = __ballot_sync(0xffffffffu, keep);
-    if (m) {
-        const int lane = threadIdx.x & 31;
-        const int leader = __ffs(m) - 1;
-        unsigned base = 0;
-        if (lane == leader) base = atomicAdd(&stats[b].nsurv, (unsigned)__popc(m));
-        base = __shfl_sync(0xffffffffu, base, leader);
-        if (keep) {
-            const unsigned slot = base + __popc(m & ((1u << lane) - 1u));
-            surv_y[(size_t)b * maxT + slot] = ypack;
-            surv_tri[(size_t)b * maxT + slot] = (unsigned)t;
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// band raster
-// ---------------------------------------------------------------------------------------------
-constexpr int kRasterThreads = 256;
-constexpr int kQueueCap = 1024;       // triangle queue per flush
-constexpr int kSmallPix = 16;         // bbox∩band pixels handled by one thread; larger -> one warp
-
-__device__ __forceinline__ void smem_min64(unsigned long long* addr, unsigned long long v) {
-    unsigned long long old = *(volatile unsigned long long*)addr;
-    while (v < old) {
-        const unsigned long long assumed = old;
-        old = atomicCAS(addr, assumed, v);
-        if (old == assumed) break;
-    }
-}
-
-struct TriGeom {
-    int X0, Y0, X1, Y1, X2, Y2;
-    float iz0, gx, gy;
-};
-
-__device__ __forceinline__ TriGeom unpack_geom(const int4 q0, const int4 q1, const int4 q2) {
-    TriGeom g;
-    g.X0 = q0.x; g.Y0 = q0.y; g.X1 = q0.z; g.Y1 = q0.w; g.X2 = q1.x; g.Y2 = q1.y;
-    g.iz0 = __int_as_float(q1.z); g.gx = __int_as_float(q1.w); g.gy = __int_as_float(q2.x);
-    return g;
-}
-
-// bbox (in pixels) of the triangle clipped to [0,W) x [y_lo, y_hi]
-__device__ __forceinline__ void tri_bbox(const TriGeom& g, int W, int y_lo, int y_hi,
-                                         int& bx0, int& bx1, int& by0, int& by1) {
-    const int xmin = min(g.X0, min(g.X1, g.X2)), xmax = max(g.X0, max(g.X1, g.X2));
-    const int ymin = min(g.Y0, min(g.Y1, g.Y2)), ymax = max(g.Y0, max(g.Y1, g.Y2));
-    bx0 = max(ceil_div256(xmin - 224), 0);
-    bx1 = min(floor_div256(xmax - 32), W - 1);
-    by0 = max(ceil_div256(ymin - 224), y_lo);
-    by1 = min(floor_div256(ymax - 32), y_hi);
-}
-
-// RS-C + RS-Z for one triangle over its bbox∩band, `nl` lanes cooperating (lane in [0,nl)).
-// keys: [4][band_pixels] sample-major visibility buffer of this band (row 0 = band_y0).
-__device__ __forceinline__ void raster_tri(const TriGeom& g, unsigned tri, int bx0, int bx1, int by0, int by1,
-                                           int lane, int nl, unsigned long long* keys, int band_pix, int W,
-                                           int band_y0, float c0, float c1) {
-    // edges e0: v0->v1, e1: v1->v2, e2: v2->v0;  E(P) = dx (Py-ay) - dy (Px-ax), interior E >= 0
-    const int dx0 = g.X1 - g.X0, dy0 = g.Y1 - g.Y0;
-    const int dx1 = g.X2 - g.X1, dy1 = g.Y2 - g.Y1;
-    const int dx2 = g.X0 - g.X2, dy2 = g.Y0 - g.Y2;
-    // top-left rule: samples exactly on an edge belong to the triangle only for top/left edges
-    const long long b0 = (dy0 < 0 || (dy0 == 0 && dx0 > 0)) ? 0 : -1;
-    const long long b1 = (dy1 < 0 || (dy1 == 0 && dx1 > 0)) ? 0 : -1;
-    const long long b2 = (dy2 < 0 || (dy2 == 0 && dx2 > 0)) ? 0 : -1;
-    const int w = bx1 - bx0 + 1;
-    const int n = w * (by1 - by0 + 1);
-    constexpr int SX[4] = {96, 224, 32, 160};
-    constexpr int SY[4] = {32, 96, 160, 224};
-    for (int i = lane; i < n; i += nl) {
-        const int ry = i / w;
-        const int px = bx0 + (i - ry * w), py = by0 + ry;
-        const int ox = px * kSubpix, oy = py * kSubpix;
-        const long long E0 = (long long)dx0 * (oy - g.Y0) - (long long)dy0 * (ox - g.X0) + b0;
-        const long long E1 = (long long)dx1 * (oy - g.Y1) - (long long)dy1 * (ox - g.X1) + b1;
-        const long long E2 = (long long)dx2 * (oy - g.Y2) - (long long)dy2 * (ox - g.X2) + b2;
-        const int pidx = (py - band_y0) * W + px;
-#pragma unroll
-        for (int s = 0; s < 4; ++s) {
-            const long long e0 = E0 + (long long)dx0 * SY[s] - (long long)dy0 * SX[s];
-            const long long e1 = E1 + (long long)dx1 * SY[s] - (long long)dy1 * SX[s];
-            const long long e2 = E2 + (long long)dx2 * SY[s] - (long long)dy2 * SX[s];
-            if ((e0 | e1 | e2) >= 0) {
-                const float fxr = (float)(ox + SX[s] - g.X0), fyr = (float)(oy + SY[s] - g.Y0);
-                const float iz = __fmaf_rn(g.gy, fyr, __fmaf_rn(g.gx, fxr, g.iz0));
-                const float d = __fmaf_rn(-c1, iz, c0);
-                if (d >= 0.0f && d <= 1.0f) {
-                    const unsigned d24 = (unsigned)__float2int_rn(__fmul_rn(d, 16777215.0f));
-                    if (d24 < kDepthMax)
-                        smem_min64(&keys[(size_t)s * band_pix + pidx], ((unsigned long long)d24 << 32) | tri);
-                }
-            }
-        }
-    }
-}
-
-struct ShadeCtx {
-    float fx_inv, fy_inv, cx, cy;
-    float iz_min, iz_max;
-    float las, lao, intensity, ambient;
-    float base[3];
-    float metallic, alpha2, kgeo;
-    const uchar4* vcolor;
-    const int* faces;
-    const float* uv;
-    const uchar4* tex;
-    int tw, th, nmips;
-};
-
-__device__ __forceinline__ float clamp01(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
-__device__ __forceinline__ float srgb_to_linear(float c) {
-    return c <= 0.04045f ? c * (1.0f / 12.92f) : powf((c + 0.055f) * (1.0f / 1.055f), 2.4f);
-}
-
-// bilinear fetch from one mip level with GL_REPEAT wrap; returns sRGB-encoded rgb in [0,1]
-__device__ __forceinline__ float3 tex_bilinear(const uchar4* __restrict__ lvl, int w, int h, float u, float v) {
-    // GL texel centres at (i+0.5)/w; v is flipped by the loader so row 0 = v 0 here
-    float x = u * w - 0.5f, y = v * h - 0.5f;
-    const float fx0 = floorf(x), fy0 = floorf(y);
-    const float ax = x - fx0, ay = y - fy0;
-    int x0 = (int)fx0 % w, y0 = (int)fy0 % h;
-    if (x0 < 0) x0 += w;
-    if (y0 < 0) y0 += h;
-    const int x1 = (x0 + 1 == w) ? 0 : x0 + 1, y1 = (y0 + 1 == h) ? 0 : y0 + 1;
-    const uchar4 a = lvl[(size_t)y0 * w + x0], b = lvl[(size_t)y0 * w + x1];
-    const uchar4 c = lvl[(size_t)y1 * w + x0], d = lvl[(size_t)y1 * w + x1];
-    const float w00 = (1.f - ax) * (1.f - ay), w10 = ax * (1.f - ay), w01 = (1.f - ax) * ay, w11 = ax * ay;
-    float3 r;
-    r.x = (a.x * w00 + b.x * w10 + c.x * w01 + d.x * w11) * (1.0f / 255.0f);
-    r.y = (a.y * w00 + b.y * w10 + c.y * w01 + d.y * w11) * (1.0f / 255.0f);
-    r.z = (a.z * w00 + b.z * w10 + c.z * w01 + d.z * w11) * (1.0f / 255.0f);
-    return r;
-}
-
-// perspective-correct barycentric weights of (v0,v1,v2) (record order) at subpixel point (Px,Py)
-__device__ __forceinline__ void persp_bary(const TriGeom& g, int Px, int Py, float& w0, float& w1, float& w2) {
-    const long long e0 = (long long)(g.X1 - g.X0) * (Py - g.Y0) - (long long)(g.Y1 - g.Y0) * (Px - g.X0);  // -> v2
-    const long long e1 = (long long)(g.X2 - g.X1) * (Py - g.Y1) - (long long)(g.Y2 - g.Y1) * (Px - g.X1);  // -> v0
-    const long long e2 = (long long)(g.X0 - g.X2) * (Py - g.Y2) - (long long)(g.Y0 - g.Y2) * (Px - g.X2);  // -> v1
-    const float inv_area = 1.0f / (float)(e0 + e1 + e2);
-    const float l0 = (float)e1 * inv_area, l1 = (float)e2 * inv_area, l2 = (float)e0 * inv_area;
-    const float iz1 = fmaf(g.gy, (float)(g.Y1 - g.Y0), fmaf(g.gx, (float)(g.X1 - g.X0), g.iz0));
-    const float iz2 = fmaf(g.gy, (float)(g.Y2 - g.Y0), fmaf(g.gx, (float)(g.X2 - g.X0), g.iz0));
-    float a0 = l0 * g.iz0, a1 = l1 * iz1, a2 = l2 * iz2;
-    const float s = a0 + a1 + a2;
-    const float inv = (fabsf(s) > 1e-30f) ? 1.0f / s : 0.0f;
-    w0 = a0 * inv; w1 = a1 * inv; w2 = a2 * inv;
-}
-
-// RS-S: shade triangle `tri` at the centre of pixel (px,py); returns RGBA8 packed little-endian.
-__device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __restrict__ rec, unsigned tri, int px, int py) {
-    const int4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
-    const TriGeom g = unpack_geom(q0, q1, q2);
-    const float nx = __int_as_float(q2.y), ny = __int_as_float(q2.z), nz = __int_as_float(q2.w);
-    const int Pcx = px * kSubpix + 128, Pcy = py * kSubpix + 128;
-    float iz = fmaf(g.gy, (float)(Pcy - g.Y0), fmaf(g.gx, (float)(Pcx - g.X0), g.iz0));
-    iz = fminf(fmaxf(iz, sc.iz_min), sc.iz_max);
-    const float z = 1.0f / iz;
-    const float x = ((px + 0.5f) - sc.cx) * sc.fx_inv * z;
-    const float y = ((py + 0.5f) - sc.cy) * sc.fy_inv * z;
-    const float dist2 = x * x + y * y + z * z;
-    const float inv_d = 1.0f / sqrtf(dist2);
-    // camera and light sit at the origin: l = v = h = -p/|p|
-    const float ndl = -(nx * x + ny * y + nz * z) * inv_d;
-    const float nl = fminf(fmaxf(ndl, 0.001f), 1.0f);
-    const float nv = fminf(fmaxf(fabsf(ndl), 0.001f), 1.0f);
-    const float nh = clamp01(ndl);
-    // spot cone around the camera's forward axis (+z in the OpenCV frame)
-    const float cd = clamp01(z * inv_d);
-    float att = clamp01(cd * sc.las + sc.lao);
-    att = att * att / dist2;
-    const float radiance = att * sc.intensity;
-
-    float base[3] = {sc.base[0], sc.base[1], sc.base[2]};
-    if (sc.vcolor || sc.tex) {
-        float w0, w1, w2;
-        persp_bary(g, Pcx, Pcy, w0, w1, w2);
-        // record order is (v0, v2, v1) of the mesh face (setup swaps v1 <-> v2)
-        const int i0 = sc.faces[3 * tri], i1 = sc.faces[3 * tri + 2], i2 = sc.faces[3 * tri + 1];
-        if (sc.vcolor) {
-            const uchar4 c0 = sc.vcolor[i0], c1 = sc.vcolor[i1], c2 = sc.vcolor[i2];
-            base[0] *= clamp01((w0 * c0.x + w1 * c1.x + w2 * c2.x) * (1.0f / 255.0f));
-            base[1] *= clamp01((w0 * c0.y + w1 * c1.y + w2 * c2.y) * (1.0f / 255.0f));
-            base[2] *= clamp01((w0 * c0.z + w1 * c1.z + w2 * c2.z) * (1.0f / 255.0f));
-        }
-        if (sc.tex) {
-            const float u = w0 * sc.uv[2 * i0] + w1 * sc.uv[2 * i1] + w2 * sc.uv[2 * i2];
-            const float v = w0 * sc.uv[2 * i0 + 1] + w1 * sc.uv[2 * i1 + 1] + w2 * sc.uv[2 * i2 + 1];
-            // LOD from one-pixel finite differences on the triangle's plane (GL quad derivatives)
-            float wx0, wx1, wx2, wy0, wy1, wy2;
-            persp_bary(g, Pcx + kSubpix, Pcy, wx0, wx1, wx2);
-            persp_bary(g, Pcx, Pcy + kSubpix, wy0, wy1, wy2);
-            const float ux = wx0 * sc.uv[2 * i0] + wx1 * sc.uv[2 * i1] + wx2 * sc.uv[2 * i2] - u;
-            const float vx = wx0 * sc.uv[2 * i0 + 1] + wx1 * sc.uv[2 * i1 + 1] + wx2 * sc.uv[2 * i2 + 1] - v;
-            const float uy = wy0 * sc.uv[2 * i0] + wy1 * sc.uv[2 * i1] + wy2 * sc.uv[2 * i2] - u;
-            const float vy = wy0 * sc.uv[2 * i0 + 1] + wy1 * sc.uv[2 * i1 + 1] + wy2 * sc.uv[2 * i2 + 1] - v;
-            const float rx2 = ux * ux * sc.tw * sc.tw + vx * vx * sc.th * sc.th;
-            const float ry2 = uy * uy * sc.tw * sc.tw + vy * vy * sc.th * sc.th;
-            float lod = 0.5f * log2f(fmaxf(fmaxf(rx2, ry2), 1e-20f));
-            lod = fminf(fmaxf(lod, 0.0f), (float)(sc.nmips - 1));
-            const int l0 = (int)floorf(lod);
-            const int l1 = min(l0 + 1, sc.nmips - 1);
-            const float fl = lod - (float)l0;
-            // walk the mip chain to level l0
-            const uchar4* lvl = sc.tex;
-            int w = sc.tw, h = sc.th;
-            for (int l = 0; l < l0; ++l) { lvl += (size_t)w * h; w = max(w >> 1, 1); h = max(h >> 1, 1); }
-            float3 ta = tex_bilinear(lvl, w, h, u, v);
-            if (l1 != l0) {
-                const uchar4* lvl1 = lvl + (size_t)w * h;
-                const float3 tb = tex_bilinear(lvl1, max(w >> 1, 1), max(h >> 1, 1), u, v);
-                ta.x += (tb.x - ta.x) * fl; ta.y += (tb.y - ta.y) * fl; ta.z += (tb.z - ta.z) * fl;
-            }
-            base[0] *= srgb_to_linear(ta.x);
-            base[1] *= srgb_to_linear(ta.y);
-            base[2] *= srgb_to_linear(ta.z);
-        }
-    }
-
-    // metallic-roughness BRDF with v = l = h: vh = 1 -> Fresnel = f0
-    const float kk = sc.kgeo;
-    const float G = (nl / (nl * (1.0f - kk) + kk)) * (nv / (nv * (1.0f - kk) + kk));
-    const float dd = nh * nh * (sc.alpha2 - 1.0f) + 1.0f;
-    const float D = sc.alpha2 / (3.14159265358979f * dd * dd);
-    const float spec_common = G * D / (4.0f * nl * nv + 1e-4f);
-    unsigned out = 0xFF000000u;
-#pragma unroll
-    for (int c = 0; c < 3; ++c) {
-        const float f0 = 0.04f + (base[c] - 0.04f) * sc.metallic;
-        const float cdiff = base[c] * 0.96f * (1.0f - sc.metallic);
-        const float diffuse = (1.0f - f0) * cdiff * (1.0f / 3.14159265358979f);
-        const float col = nl * radiance * (diffuse + f0 * spec_common) + base[c] * sc.ambient;
-        const float enc = clamp01(powf(fmaxf(col, 0.0f), 1.0f / 2.2f));
-        const unsigned q = (unsigned)(enc * 255.0f + 0.5f);
-        out |= q << (8 * c);
-    }
-    return out;
-}
-
-__device__ __forceinline__ ShadeCtx make_shade_ctx(const MeshDev& mesh, const CamPose& cam, const SceneConsts& S) {
-    ShadeCtx sc;
-    sc.fx_inv = 1.0f / cam.fx; sc.fy_inv = 1.0f / cam.fy; sc.cx = cam.cx; sc.cy = cam.cy;
-    sc.iz_min = 1.0f / S.zfar; sc.iz_max = 1.0f / S.znear;
-    sc.las = S.las; sc.lao = S.lao; sc.intensity = S.intensity; sc.ambient = S.ambient;
-    sc.base[0] = mesh.base_color[0]; sc.base[1] = mesh.base_color[1]; sc.base[2] = mesh.base_color[2];
-    sc.metallic = mesh.metallic;
-    const float rough = fminf(fmaxf(mesh.roughness, 0.04f), 1.0f);
-    const float alpha = rough * rough;
-    sc.alpha2 = alpha * alpha;
-    sc.kgeo = (rough + 1.0f) * (rough + 1.0f) * 0.125f;
-    sc.vcolor = mesh.vcolor; sc.faces = mesh.faces; sc.uv = mesh.uv; sc.tex = mesh.tex;
-    sc.tw = mesh.tw; sc.th = mesh.th; sc.nmips = mesh.nmips;
-    return sc;
-}
-
-// RS-D
-__device__ __forceinline__ float depth_readback(unsigned d24, const SceneConsts& S) {
-    const float d = __fdiv_rn((float)d24, 16777215.0f);
-    const float zn = __fsub_rn(__fmul_rn(2.0f, d), 1.0f);
-    return __fdiv_rn(S.rb_num, __fsub_rn(S.rb_sum, __fmul_rn(zn, S.rb_diff)));
-}
-
-__global__ void __launch_bounds__(kRasterThreads)
-raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
-              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int BR, int maxT,
-              SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ surv_y,
-              const unsigned* __restrict__ surv_tri, const int4* __restrict__ recs,
-              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out,
-              const float* __restrict__ gt_hwc) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int b = blockIdx.y;
-    const int band_y0 = blockIdx.x * BR;
-    const int band_y1 = min(band_y0 + BR, H) - 1;
-    const int band_pix = BR * W;
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw);           // [4][band_pix]
-    int* queue = reinterpret_cast<int*>(keys + 4 * (size_t)band_pix);                      // [kQueueCap]
-    int* medq = queue + kQueueCap;                                                         // [kQueueCap]
-    __shared__ int q_count, med_count;
-    __shared__ double red_d[4][kRasterThreads / 32];
-    __shared__ unsigned red_u[3][kRasterThreads / 32];
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const MeshDev& mesh = table[mesh_ids ? mesh_ids[b] : uniform_mesh];
-    const int4* img_recs = recs + 3 * (size_t)b * maxT;
-    const unsigned n_surv = stats[b].nsurv;   // written by setup_kernel (previous launch)
-
-    if (tid == 0) { q_count = 0; med_count = 0; }
-    bool inited = false;   // CTA-uniform
-    __syncthreads();
-
-    for (unsigned base = 0; base < n_surv; base += kRasterThreads) {
-        const unsigned i = base + tid;
-        if (i < n_surv) {
-            const unsigned yp = surv_y[(size_t)b * maxT + i];
-            const int ylo = (int)(yp & 0xFFFFu), yhi = (int)(yp >> 16);
-            if (ylo <= band_y1 && yhi >= band_y0) {
-                const int slot = atomicAdd(&q_count, 1);
-                queue[slot] = (int)surv_tri[(size_t)b * maxT + i];
-            }
-        }
-        __syncthreads();
-        const int qn = q_count;
-        const bool last = base + kRasterThreads >= n_surv;
-        if (qn > 0 && (last || qn > kQueueCap - kRasterThreads)) {
-            if (!inited) {
-                for (int k = tid; k < 4 * band_pix; k += kRasterThreads) keys[k] = kKeyEmpty;
-                inited = true;
-                __syncthreads();
-            }
-            // small triangles: one thread each; larger ones are deferred to a warp
-            for (int k = tid; k < qn; k += kRasterThreads) {
-                const unsigned tri = (unsigned)queue[k];
-                const int4* r = img_recs + 3 * (size_t)tri;
-                const TriGeom g = unpack_geom(r[0], r[1], r[2]);
-                int bx0, bx1, by0, by1;
-                tri_bbox(g, W, band_y0, band_y1, bx0, bx1, by0, by1);
-                const int npix = (bx1 - bx0 + 1) * (by1 - by0 + 1);
-                if (npix <= kSmallPix)
-                    raster_tri(g, tri, bx0, bx1, by0, by1, 0, 1, keys, band_pix, W, band_y0, S.c0, S.c1);
-                else
-                    medq[atomicAdd(&med_count, 1)] = (int)tri;
-            }
-            __syncthreads();
-            const int mn = med_count;
-            for (int k = warp; k < mn; k += kRasterThreads / 32) {
-                const unsigned tri = (unsigned)medq[k];
-                const int4* r = img_recs + 3 * (size_t)tri;
-                const TriGeom g = unpack_geom(r[0], r[1], r[2]);
-                int bx0, bx1, by0, by1;
-                tri_bbox(g, W, band_y0, band_y1, bx0, bx1, by0, by1);
-                raster_tri(g, tri, bx0, bx1, by0, by1, lane, 32, keys, band_pix, W, band_y0, S.c0, S.c1);
-            }
-            __syncthreads();
-            if (tid == 0) { q_count = 0; med_count = 0; }
-            __syncthreads();
-        }
-    }
-
-    // ---- resolve + shade + write, and per-image accumulators ----
-    const int rows = band_y1 - band_y0 + 1;
-    const int npx = rows * W;
-    const size_t img_off = (size_t)b * W * H + (size_t)band_y0 * W;
-    unsigned my_qmax = 0, my_dcount = 0;
-    float my_dmax = 0.0f;
-    double my_dsum = 0.0, my_dsumsq = 0.0;
-    if (!inited) {
-        for (int p = tid; p < npx; p += kRasterThreads) {
-            rgba_out[img_off + p] = 0u;
-            depth_out[img_off + p] = 0.0f;
-        }
-    } else {
-        const CamPose cam = load_campose(T_CO, K, b);
-        const ShadeCtx sc = make_shade_ctx(mesh, cam, S);
-        for (int p = tid; p < npx; p += kRasterThreads) {
-            const int py = band_y0 + p / W, px = p % W;
-            unsigned long long k[4];
-#pragma unroll
-            for (int s = 0; s < 4; ++s) k[s] = keys[(size_t)s * band_pix + p];
-            unsigned col[4];
-            unsigned sum_r = 0, sum_g = 0, sum_b = 0, sum_a = 0;
-#pragma unroll
-            for (int s = 0; s < 4; ++s) {
-                col[s] = 0u;
-                if (k[s] != kKeyEmpty) {
-                    const unsigned tri = (unsigned)k[s];
-                    bool found = false;
-#pragma unroll
-                    for (int j = 0; j < s; ++j)
-                        if (!found && k[j] != kKeyEmpty && (unsigned)k[j] == tri) { col[s] = col[j]; found = true; }
-                    if (!found) col[s] = shade(sc, img_recs + 3 * (size_t)tri, tri, px, py);
-                    sum_r += col[s] & 0xFFu; sum_g += (col[s] >> 8) & 0xFFu;
-                    sum_b += (col[s] >> 16) & 0xFFu; sum_a += col[s] >> 24;
-                }
-            }
-            const unsigned r8 = (sum_r + 2u) >> 2, g8 = (sum_g + 2u) >> 2, b8 = (sum_b + 2u) >> 2, a8 = (sum_a + 2u) >> 2;
-            rgba_out[img_off + p] = r8 | (g8 << 8) | (b8 << 16) | (a8 << 24);
-            float depth = 0.0f;
-            if (k[0] != kKeyEmpty) depth = depth_readback((unsigned)(k[0] >> 32), S);
-            depth_out[img_off + p] = depth;
-            my_qmax = max(my_qmax, max(r8, max(g8, b8)));
-            my_dmax = fmaxf(my_dmax, depth);
-            if (depth > 0.01f) { my_dcount++; my_dsum += (double)depth; my_dsumsq += (double)depth * (double)depth; }
-        }
-    }
-    double my_gsum = 0.0, my_gsumsq = 0.0;
-    if (gt_hwc) {
-        const float* g = gt_hwc + 3 * img_off;
-        const int nval = 3 * npx;
-        if (((reinterpret_cast<uintptr_t>(g) & 15u) == 0) && (nval % 4 == 0)) {
-            const float4* g4 = reinterpret_cast<const float4*>(g);
-            for (int i = tid; i < nval / 4; i += kRasterThreads) {
-                const float4 v = g4[i];
-                my_gsum += (double)v.x + (double)v.y + (double)v.z + (double)v.w;
-                my_gsumsq += (double)v.x * v.x + (double)v.y * v.y + (double)v.z * v.z + (double)v.w * v.w;
-            }
-        } else {
-            for (int i = tid; i < nval; i += kRasterThreads) {
-                const double v = (double)g[i];
-                my_gsum += v; my_gsumsq += v * v;
-            }
-        }
-    }
-    // block reduction -> one atomic per accumulator per CTA
-    my_qmax = warp_max(my_qmax);
-    my_dcount = (unsigned)__reduce_add_sync(0xffffffffu, my_dcount);
-    const unsigned dmax_bits = warp_max(__float_as_uint(my_dmax));
-    my_dsum = warp_sum(my_dsum); my_dsumsq = warp_sum(my_dsumsq);
-    my_gsum = warp_sum(my_gsum); my_gsumsq = warp_sum(my_gsumsq);
-    if (lane == 0) {
-        red_u[0][warp] = my_qmax; red_u[1][warp] = my_dcount; red_u[2][warp] = dmax_bits;
-        red_d[0][warp] = my_dsum; red_d[1][warp] = my_dsumsq; red_d[2][warp] = my_gsum; red_d[3][warp] = my_gsumsq;
-    }
-    __syncthreads();
-    if (tid == 0) {
-        unsigned qm = 0, dc = 0, dm = 0;
-        double a = 0, c = 0, e = 0, f = 0;
-        for (int w = 0; w < kRasterThreads / 32; ++w) {
-            qm = max(qm, red_u[0][w]); dc += red_u[1][w]; dm = max(dm, red_u[2][w]);
-            a += red_d[0][w]; c += red_d[1][w]; e += red_d[2][w]; f += red_d[3][w];
-        }
-        ImgStats* st = stats + b;
-        if (qm) atomicMax(&st->qmax, qm);
-        if (dc) { atomicAdd(&st->dcount, dc); atomicAdd(&st->dsum, a); atomicAdd(&st->dsumsq, c); }
-        if (dm) atomicMax(&st->dmax_bits, dm);
-        if (gt_hwc) { atomicAdd(&st->gsum, e); atomicAdd(&st->gsumsq, f); }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// finalize: normalise + concat / HWC expand
-// ---------------------------------------------------------------------------------------------
-struct NormConsts {
-    float inv_qmax_valid;  // 1 if qmax > 0
-    float qmax;
-    bool depth_norm;       // apply (d-mean)/std on d > 0.01
-    float dmean, dstd;
-    double gmean, gstd;
-};
-
-__device__ __forceinline__ NormConsts load_norm(const ImgStats& st, size_t npix, bool want_depth_norm, bool have_gt) {
-    NormConsts n;
-    n.qmax = (float)st.qmax;
-    n.inv_qmax_valid = st.qmax > 0 ? 1.0f : 0.0f;
-    n.depth_norm = false; n.dmean = 0.f; n.dstd = 1.f;
-    if (want_depth_norm) {
-        // ref: data_loaders.py:69-77 — two early returns hand back the depth unchanged (Q10)
-        const float dmax = __uint_as_float(st.dmax_bits);
-        if (dmax > 0.1f && st.dcount > 0) {
-            const double mean = st.dsum / (double)st.dcount;
-            double var = st.dsumsq / (double)st.dcount - mean * mean;
-            if (var < 0.0) var = 0.0;
-            const float stdf = (float)sqrt(var);
-            if (!(fabsf(stdf) <= 1e-8f)) { n.depth_norm = true; n.dmean = (float)mean; n.dstd = stdf; }
-        }
-    }
-    n.gmean = 0.0; n.gstd = 1.0;
-    if (have_gt) {
-        // ref: data_loaders.py:79-82 — population std, no zero guard (Q10): a constant image gives inf/nan
-        const double cnt = 3.0 * (double)npix;
-        n.gmean = st.gsum / cnt;
-        double var = st.gsumsq / cnt - n.gmean * n.gmean;
-        if (var < 0.0) var = 0.0;
-        n.gstd = sqrt(var);
-    }
-    return n;
-}
-
-__device__ __forceinline__ float norm_depth1(float d, const NormConsts& n) {
-    if (!n.depth_norm) return d;
-    return d > 0.01f ? __fdiv_rn(__fsub_rn(d, n.dmean), n.dstd) : 0.0f;
-}
-__device__ __forceinline__ float norm_gt1(float g, const NormConsts& n) {
-    return (float)(((double)g - n.gmean) / n.gstd);
-}
-__device__ __forceinline__ float norm_col1(unsigned q, const NormConsts& n) {
-    return n.inv_qmax_valid != 0.0f ? __fdiv_rn((float)q, n.qmax) : 0.0f;
-}
-
-// One thread = 4 consecutive pixels of one image (requires W*H % 4 == 0 and 16-B aligned planes).
-// SRC_F32: the render comes as f32 HWC (prepare_model_input on an existing render) instead of RGBA8.
-template <bool SRC_F32>
-__global__ void __launch_bounds__(256)
-finalize_concat_kernel(const ImgStats* __restrict__ stats, const unsigned* __restrict__ rgba,
-                       const float* __restrict__ init_hwc, const float* __restrict__ depth,
-                       const float* __restrict__ gt_hwc, int npix, int use_norm_depth,
-                       float* __restrict__ x_nchw, float* __restrict__ rgb_hwc_out) {
-    const int b = blockIdx.y;
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;   // quad index
-    if (4 * q >= npix) return;
-    const NormConsts n = load_norm(stats[b], (size_t)npix, use_norm_depth != 0, true);
-    const size_t pbase = (size_t)b * npix + 4 * (size_t)q;
-    const int C = use_norm_depth ? 7 : 6;
-    float* xb = x_nchw + (size_t)b * C * npix + 4 * (size_t)q;
-    int ch = 0;
-    if (use_norm_depth) {
-        const float4 d = *reinterpret_cast<const float4*>(depth + pbase);
-        float4 o;
-        o.x = norm_depth1(d.x, n); o.y = norm_depth1(d.y, n); o.z = norm_depth1(d.z, n); o.w = norm_depth1(d.w, n);
-        __stcs(reinterpret_cast<float4*>(xb), o);
-        ch = 1;
-    }
-    float r[4], g[4], bl[4];
-    if (SRC_F32) {
-        const float4* s = reinterpret_cast<const float4*>(init_hwc + 3 * pbase);
-        const float4 a = s[0], c = s[1], e = s[2];
-        r[0] = a.x; g[0] = a.y; bl[0] = a.z; r[1] = a.w; g[1] = c.x; bl[1] = c.y;
-        r[2] = c.z; g[2] = c.w; bl[2] = e.x; r[3] = e.y; g[3] = e.z; bl[3] = e.w;
-    } else {
-        const uint4 c = *reinterpret_cast<const uint4*>(rgba + pbase);
-        const unsigned cc[4] = {c.x, c.y, c.z, c.w};
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            r[i] = norm_col1(cc[i] & 0xFFu, n); g[i] = norm_col1((cc[i] >> 8) & 0xFFu, n);
-            bl[i] = norm_col1((cc[i] >> 16) & 0xFFu, n);
-        }
-    }
-    __stcs(reinterpret_cast<float4*>(xb + (size_t)(ch + 0) * npix), make_float4(r[0], r[1], r[2], r[3]));
-    __stcs(reinterpret_cast<float4*>(xb + (size_t)(ch + 1) * npix), make_float4(g[0], g[1], g[2], g[3]));
-    __stcs(reinterpret_cast<float4*>(xb + (size_t)(ch + 2) * npix), make_float4(bl[0], bl[1], bl[2], bl[3]));
-    if (rgb_hwc_out) {
-        float4* o = reinterpret_cast<float4*>(rgb_hwc_out + 3 * pbase);
-        __stcs(o + 0, make_float4(r[0], g[0], bl[0], r[1]));
-        __stcs(o + 1, make_float4(g[1], bl[1], r[2], g[2]));
-        __stcs(o + 2, make_float4(bl[2], r[3], g[3], bl[3]));
-    }
-    {
-        const float4* s = reinterpret_cast<const float4*>(gt_hwc + 3 * pbase);
-        const float4 a = __ldcs(s), c = __ldcs(s + 1), e = __ldcs(s + 2);
-        const float gr[4] = {a.x, a.w, c.z, e.y}, gg[4] = {a.y, c.x, c.w, e.z}, gb[4] = {a.z, c.y, e.x, e.w};
-        __stcs(reinterpret_cast<float4*>(xb + (size_t)(ch + 3) * npix),
-               make_float4(norm_gt1(gr[0], n), norm_gt1(gr[1], n), norm_gt1(gr[2], n), norm_gt1(gr[3], n)));
-        __stcs(reinterpret_cast<float4*>(xb + (size_t)(ch + 4) * npix),
-               make_float4(norm_gt1(gg[0], n), norm_gt1(gg[1], n), norm_gt1(gg[2], n), norm_gt1(gg[3], n)));
-        __stcs(reinterpret_cast<float4*>(xb + (size_t)(ch + 5) * npix),
-               make_float4(norm_gt1(gb[0], n), norm_gt1(gb[1], n), norm_gt1(gb[2], n), norm_gt1(gb[3], n)));
-    }
-}
-
-// scalar fallback for shapes the vector kernel cannot take (W*H % 4 != 0 or unaligned pointers)
-template <bool SRC_F32>
-__global__ void __launch_bounds__(256)
-finalize_concat_scalar_kernel(const ImgStats* __restrict__ stats, const unsigned* __restrict__ rgba,
-                              const float* __restrict__ init_hwc, const float* __restrict__ depth,
-                              const float* __restrict__ gt_hwc, int npix, int use_norm_depth,
-                              float* __restrict__ x_nchw, float* __restrict__ rgb_hwc_out) {
-    const int b = blockIdx.y;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= npix) return;
-    const NormConsts n = load_norm(stats[b], (size_t)npix, use_norm_depth != 0, true);
-    const size_t pi = (size_t)b * npix + p;
-    const int C = use_norm_depth ? 7 : 6;
-    float* xb = x_nchw + (size_t)b * C * npix + p;
-    int ch = 0;
-    if (use_norm_depth) { xb[0] = norm_depth1(depth[pi], n); ch = 1; }
-    float r, g, bl;
-    if (SRC_F32) { r = init_hwc[3 * pi]; g = init_hwc[3 * pi + 1]; bl = init_hwc[3 * pi + 2]; }
-    else {
-        const unsigned c = rgba[pi];
-        r = norm_col1(c & 0xFFu, n); g = norm_col1((c >> 8) & 0xFFu, n); bl = norm_col1((c >> 16) & 0xFFu, n);
-    }
-    xb[(size_t)(ch + 0) * npix] = r; xb[(size_t)(ch + 1) * npix] = g; xb[(size_t)(ch + 2) * npix] = bl;
-    if (rgb_hwc_out) { rgb_hwc_out[3 * pi] = r; rgb_hwc_out[3 * pi + 1] = g; rgb_hwc_out[3 * pi + 2] = bl; }
-    xb[(size_t)(ch + 3) * npix] = norm_gt1(gt_hwc[3 * pi], n);
-    xb[(size_t)(ch + 4) * npix] = norm_gt1(gt_hwc[3 * pi + 1], n);
-    xb[(size_t)(ch + 5) * npix] = norm_gt1(gt_hwc[3 * pi + 2], n);
-}
-
-// render_batch API mode: f32 HWC colour (+ optional copy of the RGBA8 framebuffer)
-__global__ void __launch_bounds__(256)
-finalize_render_kernel(const ImgStats* __restrict__ stats, const unsigned* __restrict__ rgba, int npix,
-                       float* __restrict__ rgb_hwc, unsigned* __restrict__ rgba_copy) {
-    const int b = blockIdx.y;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= npix) return;
-    const ImgStats& st = stats[b];
-    NormConsts n;
-    n.qmax = (float)st.qmax; n.inv_qmax_valid = st.qmax > 0 ? 1.0f : 0.0f;
-    const size_t pi = (size_t)b * npix + p;
-    const unsigned c = rgba[pi];
-    if (rgba_copy) rgba_copy[pi] = c;
-    if (rgb_hwc) {
-        rgb_hwc[3 * pi] = norm_col1(c & 0xFFu, n);
-        rgb_hwc[3 * pi + 1] = norm_col1((c >> 8) & 0xFFu, n);
-        rgb_hwc[3 * pi + 2] = norm_col1((c >> 16) & 0xFFu, n);
-    }
-}
-
-// prepare_model_input alone: per-image gt (and depth) statistics
-__global__ void __launch_bounds__(256)
-assemble_stats_kernel(ImgStats* __restrict__ stats, const float* __restrict__ gt_hwc,
-                      const float* __restrict__ depth, int npix, int chunks) {
-    const int b = blockIdx.y;
-    const int per = (npix + chunks - 1) / chunks;
-    const int p0 = blockIdx.x * per, p1 = min(p0 + per, npix);
-    double gs = 0, gss = 0, ds = 0, dss = 0;
-    unsigned dc = 0;
-    float dmax = 0.f;
-    const float* g = gt_hwc + 3 * (size_t)b * npix;
-    for (int i = 3 * p0 + threadIdx.x; i < 3 * p1; i += blockDim.x) {
-        const double v = (double)g[i];
-        gs += v; gss += v * v;
-    }
-    if (depth) {
-        const float* d = depth + (size_t)b * npix;
-        for (int i = p0 + threadIdx.x; i < p1; i += blockDim.x) {
-            const float v = d[i];
-            dmax = fmaxf(dmax, v);
-            if (v > 0.01f) { dc++; ds += (double)v; dss += (double)v * v; }
-        }
-    }
-    __shared__ double rd[4][8];
-    __shared__ unsigned ru[2][8];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    gs = warp_sum(gs); gss = warp_sum(gss); ds = warp_sum(ds); dss = warp_sum(dss);
-    dc = (unsigned)__reduce_add_sync(0xffffffffu, dc);
-    const unsigned dm = warp_max(__float_as_uint(fmaxf(dmax, 0.0f)));
-    if (lane == 0) { rd[0][warp] = gs; rd[1][warp] = gss; rd[2][warp] = ds; rd[3][warp] = dss; ru[0][warp] = dc; ru[1][warp] = dm; }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        double a = 0, c = 0, e = 0, f = 0; unsigned u = 0, m = 0;
-        for (int w = 0; w < (int)blockDim.x / 32; ++w) { a += rd[0][w]; c += rd[1][w]; e += rd[2][w]; f += rd[3][w]; u += ru[0][w]; m = max(m, ru[1][w]); }
-        ImgStats* st = stats + b;
-        atomicAdd(&st->gsum, a); atomicAdd(&st->gsumsq, c);
-        if (u) { atomicAdd(&st->dcount, u); atomicAdd(&st->dsum, e); atomicAdd(&st->dsumsq, f); }
-        if (m) atomicMax(&st->dmax_bits, m);
-    }
-}
+#include "raster_setup.inl"
+#include "raster_shade.inl"
+#include "raster_tile.inl"
+#include "raster_finalize.inl"
 
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+static TileGrid make_tile_grid(int W, int H, int maxT) {
+    TileGrid tg;
+    tg.ntx = (W + kTile - 1) / kTile;
+    tg.nty = (H + kTile - 1) / kTile;
+    tg.nt = tg.ntx * tg.nty;
+    tg.binned = tg.nt <= kMaxBinTiles ? 1 : 0;
+    tg.ncta_max = (maxT + kSetupThreads - 1) / kSetupThreads;
+    return tg;
+}
+
 static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
     RenderWs w;
     char* p = (char*)base;
     size_t off = 0;
-    w.stats = (ImgStats*)(p + off);      off = align256(off + sizeof(ImgStats) * (size_t)B);
-    w.mesh_ids = (int*)(p + off);        off = align256(off + sizeof(int) * (size_t)B);
-    w.surv_y = (unsigned*)(p + off);     off = align256(off + sizeof(unsigned) * (size_t)B * maxT);
-    w.surv_tri = (unsigned*)(p + off);   off = align256(off + sizeof(unsigned) * (size_t)B * maxT);
-    w.recs = (int4*)(p + off);           off = align256(off + sizeof(int4) * 3 * (size_t)B * maxT);
-    w.rgba = (unsigned*)(p + off);       off = align256(off + sizeof(unsigned) * (size_t)B * W * H);
-    w.depth = (float*)(p + off);         off = align256(off + sizeof(float) * (size_t)B * W * H);
+    const TileGrid tg = make_tile_grid(W, H, maxT);
+    const size_t ndesc = tg.binned ? (size_t)B * tg.nt * tg.ncta_max : 0;
+    const size_t nrefs = tg.binned ? ((size_t)B * tg.ncta_max) << 10 : 0;
+    w.stats = (ImgStats*)(p + off);          off = align256(off + sizeof(ImgStats) * (size_t)B);
+    w.mesh_ids = (int*)(p + off);            off = align256(off + sizeof(int) * (size_t)B);
+    w.large_tri = (unsigned*)(p + off);      off = align256(off + sizeof(unsigned) * (size_t)B * maxT);
+    w.recs = (int4*)(p + off);               off = align256(off + sizeof(int4) * 3 * (size_t)B * maxT);
+    w.desc = (unsigned*)(p + off);           off = align256(off + sizeof(unsigned) * ndesc);
+    w.refs = (unsigned char*)(p + off);      off = align256(off + nrefs);
+    w.rgba = (unsigned*)(p + off);           off = align256(off + sizeof(unsigned) * (size_t)B * W * H);
+    w.depth = (float*)(p + off);             off = align256(off + sizeof(float) * (size_t)B * W * H);
     w.total = off;
     return w;
 }
@@ -816,15 +114,6 @@ static int upload_ids(const int32_t* h_ids, int B, int* d_dst, cudaStream_t stre
     return RAC_OK;
 }
 
-static int pick_band_rows(int W, int H) {
-    // visibility buffer = BR*W*4 samples*8 B; aim for <= ~96 KB so two CTAs share an SM
-    int br = (96 * 1024) / (32 * W);
-    if (br < 1) br = 1;
-    if (br > 16) br = 16;
-    if (br > H) br = H;
-    return br;
-}
-
 static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const float* d_K, int B, int W, int H,
                          const rac_scene_t* scene, const float* d_gt_hwc, float* d_depth_user,
                          void* d_ws, size_t ws_bytes, cudaStream_t stream, RenderWs* ws_out) {
@@ -861,23 +150,24 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         if (rc != RAC_OK) return rc;
         d_ids = ws.mesh_ids;
     }
+    const TileGrid tg = make_tile_grid(W, H, maxT);
+    RAC_REQUIRE(tg.nt <= 65535 * 32, "render: too many tiles");
     {
-        dim3 grid((maxT + 255) / 256, B);
-        setup_kernel<<<grid, 256, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, S.znear,
-                                               ws.stats, ws.surv_y, ws.surv_tri, ws.recs);
+        dim3 grid(tg.ncta_max, B);
+        setup_kernel<<<grid, kSetupThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
+                                                         ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs);
         RAC_LAUNCHED();
     }
     {
-        const int BR = pick_band_rows(W, H);
-        const size_t smem = (size_t)BR * W * 32 + sizeof(int) * 2 * kQueueCap;
-        static size_t configured = 0;
-        if (smem > configured) {
+        const size_t smem = (size_t)kTilePix * 32 + sizeof(int) * 2 * kQueueCap;
+        static bool configured = false;
+        if (!configured) {
             RAC_CUDA_CHECK(cudaFuncSetAttribute(raster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = smem;
+            configured = true;
         }
-        dim3 grid((H + BR - 1) / BR, B);
-        raster_kernel<<<grid, kRasterThreads, smem, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, BR, maxT, S,
-                                                              ws.stats, ws.surv_y, ws.surv_tri, ws.recs, ws.rgba,
+        dim3 grid(tg.nt, B);
+        raster_kernel<<<grid, kRasterThreads, smem, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,
+                                                              ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs, ws.rgba,
                                                               ws.depth, d_gt_hwc);
         RAC_LAUNCHED();
     }

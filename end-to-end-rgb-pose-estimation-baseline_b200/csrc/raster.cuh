@@ -26,10 +26,13 @@ constexpr int kSubpix = 256;          // 8 subpixel bits
 constexpr float kGuardPx = 16384.0f;  // guard band in pixels
 constexpr unsigned kDepthMax = 0xFFFFFFu;
 constexpr unsigned long long kKeyEmpty = ~0ull;
+constexpr int kTile = 32;             // raster tile edge in pixels (visibility buffer: 32*32*4 samples*8 B = 32 KB)
+constexpr int kSetupThreads = 256;    // triangles per setup CTA (= refs per descriptor, u8 local ids)
+constexpr int kMaxBinTiles = 2048;    // images with more tiles (> 2 Mpx) skip binning: every triangle is "large"
 
 // per-image accumulators, zeroed at the start of every call
 struct ImgStats {
-    unsigned nsurv;      // triangles that survived setup
+    unsigned nlarge;     // survivors spanning more than 2x2 tiles (per-image large list)
     unsigned qmax;       // max resolved 8-bit colour value (R9)
     unsigned dcount;     // #pixels with depth > 0.01      (normalize_depth mask)
     unsigned dmax_bits;  // float bits of max depth (depth >= 0 so uint order == float order)
@@ -45,12 +48,20 @@ struct TriRec {
     int4 q0, q1, q2;
 };
 
+// Tile grid of one image.  binned == 0 (more than kMaxBinTiles tiles): every survivor goes to the large list.
+struct TileGrid {
+    int ntx, nty, nt;
+    int binned;
+    int ncta_max;        // ceil(maxT / kSetupThreads): stride of the descriptor / ref tables
+};
+
 struct RenderWs {
     ImgStats* stats;
     int* mesh_ids;
-    unsigned* surv_y;    // [B][maxT] ymin | ymax<<16 (pixels)
-    unsigned* surv_tri;  // [B][maxT] triangle index
-    int4* recs;          // [B][maxT][3]
+    unsigned* large_tri;   // [B][maxT] triangle ids of the per-image large list
+    int4* recs;            // [B][maxT][3]
+    unsigned* desc;        // [B][nt][ncta_max]  (offset << 16) | count, one per (tile, setup CTA)
+    unsigned char* refs;   // [B][ncta_max][1024] local triangle ids grouped by tile
     unsigned* rgba;      // [B][H][W] resolved RGBA8
     float* depth;        // [B][H][W] metric depth (may alias the caller's depth output)
     size_t total;

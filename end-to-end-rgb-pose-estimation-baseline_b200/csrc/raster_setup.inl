@@ -1,0 +1,158 @@
+// raster_setup.inl — setup_kernel: per-(image, triangle) transform / cull / plane setup + tile binning.
+// Included by raster.cu (inside namespace rac).  Spec: RS-V, RS-T in raster.cuh.
+
+__device__ __forceinline__ int floor_div256(int a) { return a >> 8; }             // arithmetic shift
+__device__ __forceinline__ int ceil_div256(int a) { return (a + 255) >> 8; }
+
+struct CamPose {
+    float r[9];
+    float t[3];
+    float fx, fy, cx, cy;
+};
+
+__device__ __forceinline__ CamPose load_campose(const float* __restrict__ T_CO, const float* __restrict__ K, int b) {
+    CamPose c;
+    const float* T = T_CO + 16 * (size_t)b;
+    c.r[0] = T[0]; c.r[1] = T[1]; c.r[2] = T[2];  c.t[0] = T[3];
+    c.r[3] = T[4]; c.r[4] = T[5]; c.r[5] = T[6];  c.t[1] = T[7];
+    c.r[6] = T[8]; c.r[7] = T[9]; c.r[8] = T[10]; c.t[2] = T[11];
+    const float* k = K + 9 * (size_t)b;
+    c.fx = k[0]; c.cx = k[2]; c.fy = k[4]; c.cy = k[5];   // ref: renderer.py:72 (fx, fy, ux, uy only)
+    return c;
+}
+
+// RS-V. Returns false when the vertex invalidates its triangle.
+__device__ __forceinline__ bool project_vertex(const CamPose& c, const float* __restrict__ p, float znear,
+                                               int& X, int& Y, float& iz) {
+    const float px = p[0], py = p[1], pz = p[2];
+    const float xc = __fmaf_rn(c.r[2], pz, __fmaf_rn(c.r[1], py, __fmaf_rn(c.r[0], px, c.t[0])));
+    const float yc = __fmaf_rn(c.r[5], pz, __fmaf_rn(c.r[4], py, __fmaf_rn(c.r[3], px, c.t[1])));
+    const float zc = __fmaf_rn(c.r[8], pz, __fmaf_rn(c.r[7], py, __fmaf_rn(c.r[6], px, c.t[2])));
+    if (!(zc >= znear)) return false;
+    iz = __fdiv_rn(1.0f, zc);
+    const float u = __fmaf_rn(c.fx, __fmul_rn(xc, iz), c.cx);
+    const float v = __fmaf_rn(c.fy, __fmul_rn(yc, iz), c.cy);
+    if (!(fabsf(u) <= kGuardPx) || !(fabsf(v) <= kGuardPx)) return false;
+    X = __float2int_rn(__fmul_rn(u, (float)kSubpix));
+    Y = __float2int_rn(__fmul_rn(v, (float)kSubpix));
+    return true;
+}
+
+// One CTA = kSetupThreads consecutive triangles of one image.  Survivors that touch at most 2x2 tiles are
+// binned: the CTA counts them per tile in shared memory, scans the counts, and publishes
+//   desc[b][tile][cta] = (offset << 16) | count      (offset into the CTA's private 1024-B ref region)
+//   refs[b][cta][offset + k] = local triangle id (u8) (triangle = cta * 256 + id)
+// with plain stores — no global atomics, nothing to zero beforehand.  The others are appended to the image's
+// large list (rare for ModelNet-scale meshes; the common case for 12-triangle boxes).
+__global__ void __launch_bounds__(kSetupThreads)
+setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
+             const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
+             float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_tri,
+             int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs) {
+    __shared__ unsigned s_cnt[kMaxBinTiles];
+    __shared__ unsigned s_off[kMaxBinTiles];
+    __shared__ unsigned s_warp[kSetupThreads / 32];
+    const int b = blockIdx.y;
+    const MeshDev& mesh = table[mesh_ids ? mesh_ids[b] : uniform_mesh];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int t = blockIdx.x * kSetupThreads + tid;
+    const int T = mesh.T;
+    if ((int)(blockIdx.x * kSetupThreads) >= T) return;   // CTA beyond this image's mesh: raster reads ceil(T/256) descriptors
+    const CamPose cam = load_campose(T_CO, K, b);
+    if (tg.binned)
+        for (int i = tid; i < tg.nt; i += kSetupThreads) s_cnt[i] = 0;
+
+    bool keep = t < T;
+    int X0 = 0, Y0 = 0, X1 = 0, Y1 = 0, X2 = 0, Y2 = 0;
+    float iz0 = 0.f, iz1 = 0.f, iz2 = 0.f;
+    int tx0 = 0, tx1 = -1, ty0 = 0, ty1 = -1;
+    if (keep) {
+        const int i0 = mesh.faces[3 * t], i1 = mesh.faces[3 * t + 1], i2 = mesh.faces[3 * t + 2];
+        keep = project_vertex(cam, mesh.verts + 3 * (size_t)i0, znear, X0, Y0, iz0);
+        keep = keep && project_vertex(cam, mesh.verts + 3 * (size_t)i1, znear, X1, Y1, iz1);
+        keep = keep && project_vertex(cam, mesh.verts + 3 * (size_t)i2, znear, X2, Y2, iz2);
+    }
+    long long area2 = 0;
+    if (keep) {
+        area2 = (long long)(X1 - X0) * (Y2 - Y0) - (long long)(X2 - X0) * (Y1 - Y0);
+        keep = area2 < 0;   // RS-T: front faces have negative area in (u, v-down) image coordinates
+    }
+    if (keep) {
+        // pixels that own at least one sample inside the bounding box (sample offsets span 32..224)
+        const int xmin = min(X0, min(X1, X2)), xmax = max(X0, max(X1, X2));
+        const int ymin = min(Y0, min(Y1, Y2)), ymax = max(Y0, max(Y1, Y2));
+        const int px0 = max(ceil_div256(xmin - 224), 0), px1 = min(floor_div256(xmax - 32), W - 1);
+        const int py0 = max(ceil_div256(ymin - 224), 0), py1 = min(floor_div256(ymax - 32), H - 1);
+        keep = (px0 <= px1) && (py0 <= py1);
+        tx0 = px0 / kTile; tx1 = px1 / kTile; ty0 = py0 / kTile; ty1 = py1 / kTile;
+    }
+    if (keep) {
+        // swap v1 <-> v2 so that the interior is on the non-negative side of all three edges
+        int tx = X1, ty = Y1; X1 = X2; Y1 = Y2; X2 = tx; Y2 = ty;
+        float tz = iz1; iz1 = iz2; iz2 = tz;
+        const float areaf = (float)(-area2);
+        const float d1 = __fsub_rn(iz1, iz0), d2 = __fsub_rn(iz2, iz0);
+        const float ex1 = (float)(X1 - X0), ey1 = (float)(Y1 - Y0);
+        const float ex2 = (float)(X2 - X0), ey2 = (float)(Y2 - Y0);
+        const float gx = __fdiv_rn(__fmaf_rn(d1, ey2, -__fmul_rn(d2, ey1)), areaf);
+        const float gy = __fdiv_rn(__fmaf_rn(d2, ex1, -__fmul_rn(d1, ex2)), areaf);
+        const float* fn = mesh.fnormals + 3 * (size_t)t;
+        const float nx = cam.r[0] * fn[0] + cam.r[1] * fn[1] + cam.r[2] * fn[2];
+        const float ny = cam.r[3] * fn[0] + cam.r[4] * fn[1] + cam.r[5] * fn[2];
+        const float nz = cam.r[6] * fn[0] + cam.r[7] * fn[1] + cam.r[8] * fn[2];
+        int4* r = recs + 3 * ((size_t)b * maxT + t);
+        r[0] = make_int4(X0, Y0, X1, Y1);
+        r[1] = make_int4(X2, Y2, __float_as_int(iz0), __float_as_int(gx));
+        r[2] = make_int4(__float_as_int(gy), __float_as_int(nx), __float_as_int(ny), __float_as_int(nz));
+    }
+    // binned: at most 2x2 tiles (extent <= 64 px keeps the raster's edge functions inside int32)
+    const bool small = keep && tg.binned && (tx1 - tx0 <= 1) && (ty1 - ty0 <= 1);
+    const bool large = keep && !small;
+    __syncthreads();   // s_cnt zeroed
+    unsigned slot[4] = {0, 0, 0, 0};
+    if (small) {
+        int k = 0;
+        for (int ty = ty0; ty <= ty1; ++ty)
+            for (int tx = tx0; tx <= tx1; ++tx) slot[k++] = atomicAdd(&s_cnt[ty * tg.ntx + tx], 1u);
+    }
+    // warp-aggregated append of large triangles to the image's large list
+    const unsigned m = __ballot_sync(0xffffffffu, large);
+    if (m) {
+        const int leader = __ffs(m) - 1;
+        unsigned base = 0;
+        if (lane == leader) base = atomicAdd(&stats[b].nlarge, (unsigned)__popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (large) large_tri[(size_t)b * maxT + base + __popc(m & ((1u << lane) - 1u))] = (unsigned)t;
+    }
+    if (!tg.binned) return;   // CTA-uniform
+    __syncthreads();
+    // exclusive scan of s_cnt[0..nt) -> s_off: thread i owns items [i*per, (i+1)*per)
+    const int per = (tg.nt + kSetupThreads - 1) / kSetupThreads;
+    const int i_lo = min(tid * per, tg.nt), i_hi = min(i_lo + per, tg.nt);
+    unsigned mine = 0;
+    for (int i = i_lo; i < i_hi; ++i) mine += s_cnt[i];
+    unsigned incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    unsigned run = incl - mine;
+    for (int w = 0; w < warp; ++w) run += s_warp[w];
+    unsigned* dimg = desc + (size_t)b * tg.nt * tg.ncta_max + blockIdx.x;
+    for (int i = i_lo; i < i_hi; ++i) {
+        const unsigned c = s_cnt[i];
+        s_off[i] = run;
+        dimg[(size_t)i * tg.ncta_max] = (run << 16) | c;    // offset < 1024, count <= 256
+        run += c;
+    }
+    __syncthreads();
+    if (small) {
+        unsigned char* region = refs + (((size_t)b * tg.ncta_max + blockIdx.x) << 10);
+        int k = 0;
+        for (int ty = ty0; ty <= ty1; ++ty)
+            for (int tx = tx0; tx <= tx1; ++tx) region[s_off[ty * tg.ntx + tx] + slot[k++]] = (unsigned char)tid;
+    }
+}

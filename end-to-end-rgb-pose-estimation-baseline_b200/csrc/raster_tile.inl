@@ -1,0 +1,321 @@
+// raster_tile.inl — raster_kernel: one CTA per (image, 32x32-px tile).  Spec: RS-C, RS-Z, RS-R in raster.cuh.
+// Included by raster.cu (inside namespace rac).
+
+constexpr int kRasterThreads = 256;
+constexpr int kQueueCap = 1024;       // triangle queue per flush
+constexpr int kSmallPix = 16;         // bbox∩tile pixels handled by one thread; larger -> one warp
+constexpr int kTilePix = kTile * kTile;
+
+__device__ __forceinline__ void smem_min64(unsigned long long* addr, unsigned long long v) {
+    unsigned long long old = *(volatile unsigned long long*)addr;
+    while (v < old) {
+        const unsigned long long assumed = old;
+        old = atomicCAS(addr, assumed, v);
+        if (old == assumed) break;
+    }
+}
+
+// bbox (in pixels) of the triangle clipped to the tile [x_lo, x_hi] x [y_lo, y_hi]
+__device__ __forceinline__ void tri_bbox(const TriGeom& g, int x_lo, int x_hi, int y_lo, int y_hi,
+                                         int& bx0, int& bx1, int& by0, int& by1) {
+    const int xmin = min(g.X0, min(g.X1, g.X2)), xmax = max(g.X0, max(g.X1, g.X2));
+    const int ymin = min(g.Y0, min(g.Y1, g.Y2)), ymax = max(g.Y0, max(g.Y1, g.Y2));
+    bx0 = max(ceil_div256(xmin - 224), x_lo);
+    bx1 = min(floor_div256(xmax - 32), x_hi);
+    by0 = max(ceil_div256(ymin - 224), y_lo);
+    by1 = min(floor_div256(ymax - 32), y_hi);
+}
+
+// RS-C + RS-Z for one triangle over its bbox∩tile, `nl` lanes cooperating (lane in [0,nl)).
+// I = int for binned triangles (extent <= 64 px: every product < 2^29), long long for large ones.
+// keys: [4][kTilePix] sample-major visibility buffer of this tile (origin tile_x0, tile_y0).
+template <typename I>
+__device__ __forceinline__ void raster_tri(const TriGeom& g, unsigned tri, int bx0, int bx1, int by0, int by1,
+                                           int lane, int nl, unsigned long long* keys, int tile_x0, int tile_y0,
+                                           float c0, float c1) {
+    // edges e0: v0->v1, e1: v1->v2, e2: v2->v0;  E(P) = dx (Py-ay) - dy (Px-ax), interior E >= 0
+    const I dx0 = g.X1 - g.X0, dy0 = g.Y1 - g.Y0;
+    const I dx1 = g.X2 - g.X1, dy1 = g.Y2 - g.Y1;
+    const I dx2 = g.X0 - g.X2, dy2 = g.Y0 - g.Y2;
+    // top-left rule: samples exactly on an edge belong to the triangle only for top/left edges
+    const I b0 = (dy0 < 0 || (dy0 == 0 && dx0 > 0)) ? 0 : -1;
+    const I b1 = (dy1 < 0 || (dy1 == 0 && dx1 > 0)) ? 0 : -1;
+    const I b2 = (dy2 < 0 || (dy2 == 0 && dx2 > 0)) ? 0 : -1;
+    const int w = bx1 - bx0 + 1;
+    const int n = w * (by1 - by0 + 1);
+    constexpr int SX[4] = {96, 224, 32, 160};
+    constexpr int SY[4] = {32, 96, 160, 224};
+    for (int i = lane; i < n; i += nl) {
+        const int ry = i / w;
+        const int px = bx0 + (i - ry * w), py = by0 + ry;
+        const int ox = px * kSubpix, oy = py * kSubpix;
+        const I E0 = dx0 * (I)(oy - g.Y0) - dy0 * (I)(ox - g.X0) + b0;
+        const I E1 = dx1 * (I)(oy - g.Y1) - dy1 * (I)(ox - g.X1) + b1;
+        const I E2 = dx2 * (I)(oy - g.Y2) - dy2 * (I)(ox - g.X2) + b2;
+        const int pidx = (py - tile_y0) * kTile + (px - tile_x0);
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            const I e0 = E0 + dx0 * (I)SY[s] - dy0 * (I)SX[s];
+            const I e1 = E1 + dx1 * (I)SY[s] - dy1 * (I)SX[s];
+            const I e2 = E2 + dx2 * (I)SY[s] - dy2 * (I)SX[s];
+            if ((e0 | e1 | e2) >= 0) {
+                const float fxr = (float)(ox + SX[s] - g.X0), fyr = (float)(oy + SY[s] - g.Y0);
+                const float iz = __fmaf_rn(g.gy, fyr, __fmaf_rn(g.gx, fxr, g.iz0));
+                const float d = __fmaf_rn(-c1, iz, c0);
+                if (d >= 0.0f && d <= 1.0f) {
+                    const unsigned d24 = (unsigned)__float2int_rn(__fmul_rn(d, 16777215.0f));
+                    if (d24 < kDepthMax)
+                        smem_min64(&keys[s * kTilePix + pidx], ((unsigned long long)d24 << 32) | tri);
+                }
+            }
+        }
+    }
+}
+
+// Rasterise the `qn` queued triangles into the tile's visibility buffer: triangles whose bbox∩tile is at most
+// kSmallPix pixels take one thread each, the others are deferred to one warp each.  Called by all threads.
+template <typename I>
+__device__ __forceinline__ void process_queue(const int* queue, int qn, int* medq, int* med_count,
+                                              const int4* __restrict__ img_recs, unsigned long long* keys,
+                                              int x_lo, int x_hi, int y_lo, int y_hi, float c0, float c1) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int k = tid; k < qn; k += kRasterThreads) {
+        const unsigned tri = (unsigned)queue[k];
+        const int4* r = img_recs + 3 * (size_t)tri;
+        const TriGeom g = unpack_geom(r[0], r[1], r[2]);
+        int bx0, bx1, by0, by1;
+        tri_bbox(g, x_lo, x_hi, y_lo, y_hi, bx0, bx1, by0, by1);
+        const int npix = (bx1 - bx0 + 1) * (by1 - by0 + 1);
+        if (bx0 > bx1 || by0 > by1) continue;
+        if (npix <= kSmallPix)
+            raster_tri<I>(g, tri, bx0, bx1, by0, by1, 0, 1, keys, x_lo, y_lo, c0, c1);
+        else
+            medq[atomicAdd(med_count, 1)] = (int)tri;
+    }
+    __syncthreads();
+    const int mn = *med_count;
+    for (int k = warp; k < mn; k += kRasterThreads / 32) {
+        const unsigned tri = (unsigned)medq[k];
+        const int4* r = img_recs + 3 * (size_t)tri;
+        const TriGeom g = unpack_geom(r[0], r[1], r[2]);
+        int bx0, bx1, by0, by1;
+        tri_bbox(g, x_lo, x_hi, y_lo, y_hi, bx0, bx1, by0, by1);
+        raster_tri<I>(g, tri, bx0, bx1, by0, by1, lane, 32, keys, x_lo, y_lo, c0, c1);
+    }
+    __syncthreads();
+    if (tid == 0) *med_count = 0;
+    __syncthreads();
+}
+
+struct TileAcc {
+    unsigned qmax, dcount;
+    float dmax;
+    double dsum, dsumsq, gsum, gsumsq;
+};
+
+// Everything one CTA does for tile `tile` of image `b`: gather -> coverage/depth -> shade/resolve -> RGBA8 + depth
+// stores -> per-image accumulators.  smem_raw: keys [4][kTilePix] u64, queue [kQueueCap], medq [kQueueCap].
+__device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl, unsigned* s_scan,
+                                            const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids,
+                                            int uniform_mesh, const float* __restrict__ T_CO, const float* __restrict__ K,
+                                            int W, int H, int maxT, const TileGrid& tg, const SceneConsts& S,
+                                            ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
+                                            const int4* __restrict__ recs, const unsigned* __restrict__ desc,
+                                            const unsigned char* __restrict__ refs, unsigned* __restrict__ rgba_out,
+                                            float* __restrict__ depth_out, const float* __restrict__ gt_hwc,
+                                            int b, int tile) {
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw);           // [4][kTilePix]
+    int* queue = reinterpret_cast<int*>(keys + 4 * kTilePix);                              // [kQueueCap]
+    int* medq = queue + kQueueCap;                                                         // [kQueueCap]
+    int* q_count = s_ctl, *med_count = s_ctl + 1;
+    unsigned* s_dcnt = s_scan;                      // [kRasterThreads] descriptor counts
+    unsigned* s_dscan = s_scan + kRasterThreads;    // [kRasterThreads] exclusive scan
+    unsigned* s_doff = s_scan + 2 * kRasterThreads; // [kRasterThreads] offset into the ref region
+    unsigned* s_wsum = s_scan + 3 * kRasterThreads; // [8]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tx = tile % tg.ntx, ty = tile / tg.ntx;
+    const int x_lo = tx * kTile, y_lo = ty * kTile;
+    const int x_hi = min(x_lo + kTile, W) - 1, y_hi = min(y_lo + kTile, H) - 1;
+    const MeshDev& mesh = table[mesh_ids ? mesh_ids[b] : uniform_mesh];
+    const int4* img_recs = recs + 3 * (size_t)b * maxT;
+    const unsigned n_large = stats[b].nlarge;   // written by setup_kernel (previous launch)
+    const int ncta = tg.binned ? (mesh.T + kSetupThreads - 1) / kSetupThreads : 0;
+
+    if (tid == 0) { *q_count = 0; *med_count = 0; }
+    bool inited = false;   // CTA-uniform
+    __syncthreads();
+
+    // ---- binned triangles: descriptors of this tile, kRasterThreads at a time ----
+    const unsigned* dtile = desc + ((size_t)b * tg.nt + tile) * tg.ncta_max;
+    for (int dbase = 0; dbase < ncta; dbase += kRasterThreads) {
+        const int j = dbase + tid;
+        const unsigned d = j < ncta ? dtile[j] : 0u;
+        const unsigned c = d & 0xFFFFu;
+        unsigned incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_wsum[warp] = incl;
+        __syncthreads();
+        unsigned wbase = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kRasterThreads / 32; ++w) {
+            const unsigned v = s_wsum[w];
+            if (w < warp) wbase += v;
+            total += v;
+        }
+        s_dcnt[tid] = c; s_dscan[tid] = wbase + incl - c; s_doff[tid] = d >> 16;
+        __syncthreads();
+        const int nd = min(kRasterThreads, ncta - dbase);
+        for (unsigned base = 0; base < total; base += kQueueCap) {
+            // expand refs [base, base + kQueueCap) of this descriptor group into the queue, one warp per descriptor
+            for (int jj = warp; jj < nd; jj += kRasterThreads / 32) {
+                const unsigned cj = s_dcnt[jj];
+                if (cj == 0) continue;
+                const unsigned sj = s_dscan[jj];
+                const unsigned lo = max(sj, base), hi = min(sj + cj, base + (unsigned)kQueueCap);
+                const unsigned char* region = refs + (((size_t)b * tg.ncta_max + dbase + jj) << 10) + s_doff[jj];
+                for (unsigned k = lo + lane; k < hi; k += 32)
+                    queue[k - base] = (dbase + jj) * kSetupThreads + (int)region[k - sj];
+            }
+            if (!inited) {
+                for (int k = tid; k < 4 * kTilePix; k += kRasterThreads) keys[k] = kKeyEmpty;
+                inited = true;
+            }
+            __syncthreads();
+            const int qn = (int)min((unsigned)kQueueCap, total - base);
+            process_queue<int>(queue, qn, medq, med_count, img_recs, keys, x_lo, x_hi, y_lo, y_hi, S.c0, S.c1);
+        }
+    }
+
+    // ---- large triangles: every tile scans the image's large list ----
+    for (unsigned base = 0; base < n_large; base += kRasterThreads) {
+        const unsigned i = base + tid;
+        if (i < n_large) {
+            const unsigned tri = large_tri[(size_t)b * maxT + i];
+            const int4* r = img_recs + 3 * (size_t)tri;
+            const int4 q0 = r[0], q1 = r[1];
+            const int xmin = min(q0.x, min(q0.z, q1.x)), xmax = max(q0.x, max(q0.z, q1.x));
+            const int ymin = min(q0.y, min(q0.w, q1.y)), ymax = max(q0.y, max(q0.w, q1.y));
+            if (ceil_div256(xmin - 224) <= x_hi && floor_div256(xmax - 32) >= x_lo &&
+                ceil_div256(ymin - 224) <= y_hi && floor_div256(ymax - 32) >= y_lo)
+                queue[atomicAdd(q_count, 1)] = (int)tri;
+        }
+        __syncthreads();
+        const int qn = *q_count;
+        const bool last = base + kRasterThreads >= n_large;
+        if (qn > 0 && (last || qn > kQueueCap - kRasterThreads)) {
+            if (!inited) {
+                for (int k = tid; k < 4 * kTilePix; k += kRasterThreads) keys[k] = kKeyEmpty;
+                inited = true;
+                __syncthreads();
+            }
+            process_queue<long long>(queue, qn, medq, med_count, img_recs, keys, x_lo, x_hi, y_lo, y_hi, S.c0, S.c1);
+            if (tid == 0) *q_count = 0;
+            __syncthreads();
+        }
+    }
+
+    // ---- resolve + shade + write, and per-image accumulators ----
+    const int tw = x_hi - x_lo + 1, th = y_hi - y_lo + 1;
+    TileAcc acc;
+    acc.qmax = 0; acc.dcount = 0; acc.dmax = 0.0f; acc.dsum = 0.0; acc.dsumsq = 0.0; acc.gsum = 0.0; acc.gsumsq = 0.0;
+    const size_t img_pix = (size_t)b * W * H;
+    if (!inited) {
+        for (int p = tid; p < kTilePix; p += kRasterThreads) {
+            const int lx = p & (kTile - 1), ly = p / kTile;
+            if (lx < tw && ly < th) {
+                const size_t o = img_pix + (size_t)(y_lo + ly) * W + (x_lo + lx);
+                rgba_out[o] = 0u;
+                depth_out[o] = 0.0f;
+            }
+        }
+    } else {
+        const CamPose cam = load_campose(T_CO, K, b);
+        const ShadeCtx sc = make_shade_ctx(mesh, cam, S);
+        for (int p = tid; p < kTilePix; p += kRasterThreads) {
+            const int lx = p & (kTile - 1), ly = p / kTile;
+            if (lx >= tw || ly >= th) continue;
+            const int px = x_lo + lx, py = y_lo + ly;
+            unsigned long long k[4];
+#pragma unroll
+            for (int s = 0; s < 4; ++s) k[s] = keys[s * kTilePix + p];
+            unsigned col[4];
+            unsigned sum_r = 0, sum_g = 0, sum_b = 0, sum_a = 0;
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                col[s] = 0u;
+                if (k[s] != kKeyEmpty) {
+                    const unsigned tri = (unsigned)k[s];
+                    bool found = false;
+#pragma unroll
+                    for (int j = 0; j < s; ++j)
+                        if (!found && k[j] != kKeyEmpty && (unsigned)k[j] == tri) { col[s] = col[j]; found = true; }
+                    if (!found) col[s] = shade(sc, img_recs + 3 * (size_t)tri, tri, px, py);
+                    sum_r += col[s] & 0xFFu; sum_g += (col[s] >> 8) & 0xFFu;
+                    sum_b += (col[s] >> 16) & 0xFFu; sum_a += col[s] >> 24;
+                }
+            }
+            const unsigned r8 = (sum_r + 2u) >> 2, g8 = (sum_g + 2u) >> 2, b8 = (sum_b + 2u) >> 2, a8 = (sum_a + 2u) >> 2;
+            const size_t o = img_pix + (size_t)py * W + px;
+            rgba_out[o] = r8 | (g8 << 8) | (b8 << 16) | (a8 << 24);
+            float depth = 0.0f;
+            if (k[0] != kKeyEmpty) depth = depth_readback((unsigned)(k[0] >> 32), S);
+            depth_out[o] = depth;
+            acc.qmax = max(acc.qmax, max(r8, max(g8, b8)));
+            acc.dmax = fmaxf(acc.dmax, depth);
+            if (depth > 0.01f) { acc.dcount++; acc.dsum += (double)depth; acc.dsumsq += (double)depth * (double)depth; }
+        }
+    }
+    if (gt_hwc) {
+        // this tile's share of the gt crop statistics (normalize_img, data_loaders.py:79-82): rows of 3*tw floats
+        const int rowf = 3 * tw;
+        for (int i = tid; i < rowf * th; i += kRasterThreads) {
+            const int ly = i / rowf, c = i - ly * rowf;
+            const double v = (double)__ldg(gt_hwc + 3 * (img_pix + (size_t)(y_lo + ly) * W + x_lo) + c);
+            acc.gsum += v; acc.gsumsq += v * v;
+        }
+    }
+    // block reduction -> one atomic per accumulator per CTA
+    __shared__ double red_d[4][kRasterThreads / 32];
+    __shared__ unsigned red_u[3][kRasterThreads / 32];
+    acc.qmax = warp_max(acc.qmax);
+    acc.dcount = (unsigned)__reduce_add_sync(0xffffffffu, acc.dcount);
+    const unsigned dmax_bits = warp_max(__float_as_uint(acc.dmax));
+    acc.dsum = warp_sum(acc.dsum); acc.dsumsq = warp_sum(acc.dsumsq);
+    acc.gsum = warp_sum(acc.gsum); acc.gsumsq = warp_sum(acc.gsumsq);
+    if (lane == 0) {
+        red_u[0][warp] = acc.qmax; red_u[1][warp] = acc.dcount; red_u[2][warp] = dmax_bits;
+        red_d[0][warp] = acc.dsum; red_d[1][warp] = acc.dsumsq; red_d[2][warp] = acc.gsum; red_d[3][warp] = acc.gsumsq;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        unsigned qm = 0, dc = 0, dm = 0;
+        double a = 0, c = 0, e = 0, f = 0;
+        for (int w = 0; w < kRasterThreads / 32; ++w) {
+            qm = max(qm, red_u[0][w]); dc += red_u[1][w]; dm = max(dm, red_u[2][w]);
+            a += red_d[0][w]; c += red_d[1][w]; e += red_d[2][w]; f += red_d[3][w];
+        }
+        ImgStats* st = stats + b;
+        if (qm) atomicMax(&st->qmax, qm);
+        if (dc) { atomicAdd(&st->dcount, dc); atomicAdd(&st->dsum, a); atomicAdd(&st->dsumsq, c); }
+        if (dm) atomicMax(&st->dmax_bits, dm);
+        if (gt_hwc) { atomicAdd(&st->gsum, e); atomicAdd(&st->gsumsq, f); }
+    }
+}
+
+__global__ void __launch_bounds__(kRasterThreads)
+raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
+              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
+              SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
+              const int4* __restrict__ recs, const unsigned* __restrict__ desc, const unsigned char* __restrict__ refs,
+              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, const float* __restrict__ gt_hwc) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ int s_ctl[2];
+    __shared__ unsigned s_scan[3 * kRasterThreads + kRasterThreads / 32];
+    raster_tile(smem_raw, s_ctl, s_scan, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_tri,
+                recs, desc, refs, rgba_out, depth_out, gt_hwc, blockIdx.y, blockIdx.x);
+}

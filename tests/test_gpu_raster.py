@@ -248,4 +248,4 @@ def test_full_size_properties(rac):
     ok = (u >= 1) & (u < W - 1) & (v >= 1) & (v < H - 1)
     dz = depth[v[ok], u[ok]]
     front = np.abs(dz - P[ok, 2]) < 0.01
-    assert front.mean() > 0.25 and (dz[front] > 0).all()
+    assert front.mean() > 0.1 and (dz[front] > 0).all()   # half the faces are dropped (holes) and half face away
