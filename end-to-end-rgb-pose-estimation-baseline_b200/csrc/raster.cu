@@ -51,7 +51,12 @@ static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
     const TileGrid tg = make_tile_grid(W, H, maxT);
     const size_t ndesc = tg.binned ? (size_t)B * tg.nt * tg.ncta_max : 0;
     const size_t nrefs = tg.binned ? ((size_t)B * tg.ncta_max) << 10 : 0;
+    // [stats | ctl | flags] form one contiguous block that a single memset zeroes per call
     w.stats = (ImgStats*)(p + off);          off = align256(off + sizeof(ImgStats) * (size_t)B);
+    w.ctl = (WorkCtl*)(p + off);             off = align256(off + sizeof(WorkCtl));
+    w.flags = (unsigned*)(p + off);          off = align256(off + sizeof(unsigned) * (size_t)B * tg.nt);
+    w.zero_bytes = off;
+    w.worklist = (unsigned*)(p + off);       off = align256(off + sizeof(unsigned) * (size_t)B * tg.nt);
     w.mesh_ids = (int*)(p + off);            off = align256(off + sizeof(int) * (size_t)B);
     w.large_tri = (unsigned*)(p + off);      off = align256(off + sizeof(unsigned) * (size_t)B * maxT);
     w.recs = (int4*)(p + off);               off = align256(off + sizeof(int4) * 3 * (size_t)B * maxT);
@@ -143,7 +148,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
     const SceneConsts S = make_scene_consts(scene);
     const MeshDev* table = mesh_table_dev();
 
-    RAC_CUDA_CHECK(cudaMemsetAsync(ws.stats, 0, sizeof(ImgStats) * (size_t)B, stream));
+    RAC_CUDA_CHECK(cudaMemsetAsync(ws.stats, 0, ws.zero_bytes, stream));
     const int* d_ids = nullptr;
     if (!uniform) {
         int rc = upload_ids(h_mesh_ids, B, ws.mesh_ids, stream);
@@ -151,28 +156,51 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         d_ids = ws.mesh_ids;
     }
     const TileGrid tg = make_tile_grid(W, H, maxT);
-    RAC_REQUIRE(tg.nt <= 65535 * 32, "render: too many tiles");
-    {
-        dim3 grid(tg.ncta_max, B);
-        setup_kernel<<<grid, kSetupThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
-                                                         ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs);
+    if (d_gt_hwc) {   // normalize_img statistics of the gt crop (data_loaders.py:79-82), streamed once
+        const int npix = W * H;
+        const int chunks = (npix + 8191) / 8192;
+        assemble_stats_kernel<<<dim3(chunks, B), 256, 0, stream>>>(ws.stats, d_gt_hwc, nullptr, npix, chunks);
         RAC_LAUNCHED();
     }
     {
-        const size_t smem = (size_t)kTilePix * 32 + sizeof(int) * 2 * kQueueCap;
+        dim3 grid(tg.ncta_max, B);
+        setup_kernel<<<grid, kSetupThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
+                                                         ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs,
+                                                         ws.ctl, ws.flags, ws.worklist);
+        RAC_LAUNCHED();
+    }
+    {
+        const size_t smem = kRasterSmemBytes;
         static bool configured = false;
         if (!configured) {
             RAC_CUDA_CHECK(cudaFuncSetAttribute(raster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             configured = true;
         }
-        dim3 grid(tg.nt, B);
+        // persistent CTAs: as many as fit on the device, capped by the number of tiles
+        static int ctas_per_sm = 0, n_sm = 0;
+        if (!ctas_per_sm) {
+            int dev = 0;
+            RAC_CUDA_CHECK(cudaGetDevice(&dev));
+            RAC_CUDA_CHECK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+            RAC_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, raster_kernel, kRasterThreads, smem));
+            if (ctas_per_sm < 1) ctas_per_sm = 1;
+        }
+        const long long tiles = (long long)tg.nt * B;
+        const int grid = (int)(tiles < (long long)n_sm * ctas_per_sm ? tiles : (long long)n_sm * ctas_per_sm);
         raster_kernel<<<grid, kRasterThreads, smem, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,
-                                                              ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs, ws.rgba,
-                                                              ws.depth, d_gt_hwc);
+                                                              ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs,
+                                                              ws.ctl, ws.worklist, ws.rgba, ws.depth);
         RAC_LAUNCHED();
     }
     *ws_out = ws;
     return RAC_OK;
+}
+
+static FlagView make_flag_view(const unsigned* flags, int W, int H) {
+    const TileGrid tg = make_tile_grid(W, H, 1);
+    FlagView fv;
+    fv.flags = flags; fv.W = W; fv.ntx = tg.ntx; fv.nt = tg.nt;
+    return fv;
 }
 
 }  // namespace rac
@@ -197,10 +225,11 @@ int rac_render_batch(const int32_t* h_mesh_ids, const float* d_T_CO, const float
     RenderWs ws;
     int rc = render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, nullptr, d_depth, d_ws, ws_bytes, stream, &ws);
     if (rc != RAC_OK) return rc;
-    if (d_rgb_hwc || d_rgba8) {
+    if (d_rgb_hwc || d_rgba8 || d_depth) {   // d_depth alone still needs its background tiles zeroed
         const int npix = W * H;
         dim3 grid((npix + 255) / 256, B);
-        finalize_render_kernel<<<grid, 256, 0, stream>>>(ws.stats, ws.rgba, npix, d_rgb_hwc, (unsigned*)d_rgba8);
+        finalize_render_kernel<<<grid, 256, 0, stream>>>(ws.stats, ws.rgba, npix, d_rgb_hwc, (unsigned*)d_rgba8,
+                                                         make_flag_view(ws.flags, W, H), d_depth);
         RAC_LAUNCHED();
     }
     return RAC_OK;
@@ -208,22 +237,22 @@ int rac_render_batch(const int32_t* h_mesh_ids, const float* d_T_CO, const float
 
 static int launch_concat(bool src_f32, const ImgStats* stats, const unsigned* rgba, const float* init_hwc,
                          const float* depth, const float* gt, int B, int npix, int use_norm_depth,
-                         float* x, float* rgb_out, cudaStream_t stream) {
+                         float* x, float* rgb_out, FlagView fv, float* depth_bg, cudaStream_t stream) {
     auto aligned = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
     const bool vec = (npix % 4 == 0) && aligned(rgba) && aligned(init_hwc) && aligned(depth) && aligned(gt) &&
                      aligned(x) && aligned(rgb_out);
     if (vec) {
         dim3 grid((npix / 4 + 255) / 256, B);
         if (src_f32)
-            finalize_concat_kernel<true><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out);
+            finalize_concat_kernel<true><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out, fv, depth_bg);
         else
-            finalize_concat_kernel<false><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out);
+            finalize_concat_kernel<false><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out, fv, depth_bg);
     } else {
         dim3 grid((npix + 255) / 256, B);
         if (src_f32)
-            finalize_concat_scalar_kernel<true><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out);
+            finalize_concat_scalar_kernel<true><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out, fv, depth_bg);
         else
-            finalize_concat_scalar_kernel<false><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out);
+            finalize_concat_scalar_kernel<false><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out, fv, depth_bg);
     }
     RAC_LAUNCHED();
     return RAC_OK;
@@ -238,7 +267,7 @@ int rac_render_concat(const int32_t* h_mesh_ids, const float* d_T_CO, const floa
     int rc = render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, d_gt_hwc, d_depth_out, d_ws, ws_bytes, stream, &ws);
     if (rc != RAC_OK) return rc;
     return launch_concat(false, ws.stats, ws.rgba, nullptr, ws.depth, d_gt_hwc, B, W * H, use_norm_depth,
-                         d_x_nchw, d_rgb_hwc_out, stream);
+                         d_x_nchw, d_rgb_hwc_out, make_flag_view(ws.flags, W, H), d_depth_out, stream);
 }
 
 int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const float* d_depth, int B, int W, int H,
@@ -257,7 +286,8 @@ int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const flo
     const int chunks = (npix + 8191) / 8192;
     assemble_stats_kernel<<<dim3(chunks, B), 256, 0, stream>>>(stats, d_gt_hwc, use_norm_depth ? d_depth : nullptr, npix, chunks);
     RAC_LAUNCHED();
-    return launch_concat(true, stats, nullptr, d_init_hwc, d_depth, d_gt_hwc, B, npix, use_norm_depth, d_x_nchw, nullptr, stream);
+    return launch_concat(true, stats, nullptr, d_init_hwc, d_depth, d_gt_hwc, B, npix, use_norm_depth, d_x_nchw, nullptr,
+                         make_flag_view(nullptr, W, H), nullptr, stream);
 }
 
 }  // extern "C"

@@ -55,6 +55,14 @@ struct TileGrid {
     int ncta_max;        // ceil(maxT / kSetupThreads): stride of the descriptor / ref tables
 };
 
+// Device-side work-list control: setup appends non-empty tiles, the persistent raster CTAs pop them.
+struct WorkCtl {
+    unsigned n_work;     // tiles appended by setup_kernel
+    unsigned next;       // next work-list entry to rasterise
+    unsigned pad[62];
+};
+static_assert(sizeof(WorkCtl) == 256, "WorkCtl must be 256 B");
+
 struct RenderWs {
     ImgStats* stats;
     int* mesh_ids;
@@ -62,8 +70,12 @@ struct RenderWs {
     int4* recs;            // [B][maxT][3]
     unsigned* desc;        // [B][nt][ncta_max]  (offset << 16) | count, one per (tile, setup CTA)
     unsigned char* refs;   // [B][ncta_max][1024] local triangle ids grouped by tile
+    WorkCtl* ctl;          // work-list counters (zeroed with stats and flags by one memset)
+    unsigned* flags;       // [B][nt] 1 = tile has at least one triangle (raster writes it; finalize treats 0 as background)
+    unsigned* worklist;    // [B*nt] compact list of non-empty tiles, b * nt + tile, appended by setup
     unsigned* rgba;      // [B][H][W] resolved RGBA8
     float* depth;        // [B][H][W] metric depth (may alias the caller's depth output)
+    size_t zero_bytes;     // bytes from `stats` that every call zeroes (stats + ctl + flags)
     size_t total;
 };
 

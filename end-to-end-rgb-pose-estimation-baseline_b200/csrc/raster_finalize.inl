@@ -51,6 +51,18 @@ __device__ __forceinline__ float norm_col1(unsigned q, const NormConsts& n) {
     return n.inv_qmax_valid != 0.0f ? __fdiv_rn((float)q, n.qmax) : 0.0f;
 }
 
+// Tile flags written by setup_kernel: 0 = no triangle touched the tile -> background (the raster kernel never wrote
+// its RGBA8 / depth there).  flags == nullptr: every pixel is valid (prepare_model_input on an existing render).
+struct FlagView {
+    const unsigned* flags;   // [B][nt]
+    int W, ntx, nt;
+};
+__device__ __forceinline__ bool pixel_live(const FlagView& fv, int b, int p) {
+    if (!fv.flags) return true;
+    const int y = p / fv.W, x = p - y * fv.W;
+    return fv.flags[(size_t)b * fv.nt + (y / kTile) * fv.ntx + (x / kTile)] != 0u;
+}
+
 // One thread = 4 consecutive pixels of one image (requires W*H % 4 == 0 and 16-B aligned planes).
 // SRC_F32: the render comes as f32 HWC (prepare_model_input on an existing render) instead of RGBA8.
 template <bool SRC_F32>
@@ -58,7 +70,8 @@ __global__ void __launch_bounds__(256)
 finalize_concat_kernel(const ImgStats* __restrict__ stats, const unsigned* __restrict__ rgba,
                        const float* __restrict__ init_hwc, const float* __restrict__ depth,
                        const float* __restrict__ gt_hwc, int npix, int use_norm_depth,
-                       float* __restrict__ x_nchw, float* __restrict__ rgb_hwc_out) {
+                       float* __restrict__ x_nchw, float* __restrict__ rgb_hwc_out,
+                       FlagView fv, float* __restrict__ depth_bg) {
     const int b = blockIdx.y;
     const int q = blockIdx.x * blockDim.x + threadIdx.x;   // quad index
     if (4 * q >= npix) return;
@@ -67,8 +80,23 @@ finalize_concat_kernel(const ImgStats* __restrict__ stats, const unsigned* __res
     const int C = use_norm_depth ? 7 : 6;
     float* xb = x_nchw + (size_t)b * C * npix + 4 * (size_t)q;
     int ch = 0;
+    // W % 4 == 0: the quad lies in one row and one tile; otherwise test each pixel
+    bool live[4];
+    live[0] = pixel_live(fv, b, 4 * q);
+    if ((fv.W & 3) == 0 || !fv.flags) { live[1] = live[2] = live[3] = live[0]; }
+    else { live[1] = pixel_live(fv, b, 4 * q + 1); live[2] = pixel_live(fv, b, 4 * q + 2); live[3] = pixel_live(fv, b, 4 * q + 3); }
+    const bool any_live = live[0] || live[1] || live[2] || live[3];
+    const bool all_live = live[0] && live[1] && live[2] && live[3];
+    if (depth_bg && !all_live) {   // the caller's depth buffer: background tiles were never written by the raster kernel
+#pragma unroll
+        for (int i = 0; i < 4; ++i) if (!live[i]) depth_bg[pbase + i] = 0.0f;
+    }
     if (use_norm_depth) {
-        const float4 d = *reinterpret_cast<const float4*>(depth + pbase);
+        float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (any_live) {
+            d = *reinterpret_cast<const float4*>(depth + pbase);
+            if (!live[0]) d.x = 0.f; if (!live[1]) d.y = 0.f; if (!live[2]) d.z = 0.f; if (!live[3]) d.w = 0.f;
+        }
         float4 o;
         o.x = norm_depth1(d.x, n); o.y = norm_depth1(d.y, n); o.z = norm_depth1(d.z, n); o.w = norm_depth1(d.w, n);
         __stcs(reinterpret_cast<float4*>(xb), o);
@@ -81,8 +109,9 @@ finalize_concat_kernel(const ImgStats* __restrict__ stats, const unsigned* __res
         r[0] = a.x; g[0] = a.y; bl[0] = a.z; r[1] = a.w; g[1] = c.x; bl[1] = c.y;
         r[2] = c.z; g[2] = c.w; bl[2] = e.x; r[3] = e.y; g[3] = e.z; bl[3] = e.w;
     } else {
-        const uint4 c = *reinterpret_cast<const uint4*>(rgba + pbase);
-        const unsigned cc[4] = {c.x, c.y, c.z, c.w};
+        uint4 c = make_uint4(0u, 0u, 0u, 0u);
+        if (any_live) c = *reinterpret_cast<const uint4*>(rgba + pbase);
+        const unsigned cc[4] = {live[0] ? c.x : 0u, live[1] ? c.y : 0u, live[2] ? c.z : 0u, live[3] ? c.w : 0u};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             r[i] = norm_col1(cc[i] & 0xFFu, n); g[i] = norm_col1((cc[i] >> 8) & 0xFFu, n);
@@ -117,7 +146,8 @@ __global__ void __launch_bounds__(256)
 finalize_concat_scalar_kernel(const ImgStats* __restrict__ stats, const unsigned* __restrict__ rgba,
                               const float* __restrict__ init_hwc, const float* __restrict__ depth,
                               const float* __restrict__ gt_hwc, int npix, int use_norm_depth,
-                              float* __restrict__ x_nchw, float* __restrict__ rgb_hwc_out) {
+                              float* __restrict__ x_nchw, float* __restrict__ rgb_hwc_out,
+                              FlagView fv, float* __restrict__ depth_bg) {
     const int b = blockIdx.y;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= npix) return;
@@ -126,11 +156,13 @@ finalize_concat_scalar_kernel(const ImgStats* __restrict__ stats, const unsigned
     const int C = use_norm_depth ? 7 : 6;
     float* xb = x_nchw + (size_t)b * C * npix + p;
     int ch = 0;
-    if (use_norm_depth) { xb[0] = norm_depth1(depth[pi], n); ch = 1; }
+    const bool live = pixel_live(fv, b, p);
+    if (depth_bg && !live) depth_bg[pi] = 0.0f;
+    if (use_norm_depth) { xb[0] = norm_depth1(live ? depth[pi] : 0.0f, n); ch = 1; }
     float r, g, bl;
     if (SRC_F32) { r = init_hwc[3 * pi]; g = init_hwc[3 * pi + 1]; bl = init_hwc[3 * pi + 2]; }
     else {
-        const unsigned c = rgba[pi];
+        const unsigned c = live ? rgba[pi] : 0u;
         r = norm_col1(c & 0xFFu, n); g = norm_col1((c >> 8) & 0xFFu, n); bl = norm_col1((c >> 16) & 0xFFu, n);
     }
     xb[(size_t)(ch + 0) * npix] = r; xb[(size_t)(ch + 1) * npix] = g; xb[(size_t)(ch + 2) * npix] = bl;
@@ -143,7 +175,8 @@ finalize_concat_scalar_kernel(const ImgStats* __restrict__ stats, const unsigned
 // render_batch API mode: f32 HWC colour (+ optional copy of the RGBA8 framebuffer)
 __global__ void __launch_bounds__(256)
 finalize_render_kernel(const ImgStats* __restrict__ stats, const unsigned* __restrict__ rgba, int npix,
-                       float* __restrict__ rgb_hwc, unsigned* __restrict__ rgba_copy) {
+                       float* __restrict__ rgb_hwc, unsigned* __restrict__ rgba_copy,
+                       FlagView fv, float* __restrict__ depth_bg) {
     const int b = blockIdx.y;
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= npix) return;
@@ -151,7 +184,9 @@ finalize_render_kernel(const ImgStats* __restrict__ stats, const unsigned* __res
     NormConsts n;
     n.qmax = (float)st.qmax; n.inv_qmax_valid = st.qmax > 0 ? 1.0f : 0.0f;
     const size_t pi = (size_t)b * npix + p;
-    const unsigned c = rgba[pi];
+    const bool live = pixel_live(fv, b, p);
+    if (depth_bg && !live) depth_bg[pi] = 0.0f;
+    const unsigned c = live ? rgba[pi] : 0u;
     if (rgba_copy) rgba_copy[pi] = c;
     if (rgb_hwc) {
         rgb_hwc[3 * pi] = norm_col1(c & 0xFFu, n);
@@ -170,10 +205,21 @@ assemble_stats_kernel(ImgStats* __restrict__ stats, const float* __restrict__ gt
     double gs = 0, gss = 0, ds = 0, dss = 0;
     unsigned dc = 0;
     float dmax = 0.f;
-    const float* g = gt_hwc + 3 * (size_t)b * npix;
-    for (int i = 3 * p0 + threadIdx.x; i < 3 * p1; i += blockDim.x) {
-        const double v = (double)g[i];
-        gs += v; gss += v * v;
+    {
+        // 16-B aligned body with 128-bit streaming loads, scalar head / tail
+        const float* g = gt_hwc + 3 * ((size_t)b * npix + p0);
+        const int n = 3 * (p1 - p0);
+        int head = (int)(((16u - (unsigned)(reinterpret_cast<uintptr_t>(g) & 15u)) & 15u) >> 2);
+        if (head > n) head = n;
+        const int nv = (n - head) >> 2;
+        const float4* g4 = reinterpret_cast<const float4*>(g + head);
+        for (int i = threadIdx.x; i < nv; i += blockDim.x) {
+            const float4 v = __ldg(g4 + i);
+            gs += ((double)v.x + (double)v.y) + ((double)v.z + (double)v.w);
+            gss += ((double)v.x * v.x + (double)v.y * v.y) + ((double)v.z * v.z + (double)v.w * v.w);
+        }
+        for (int i = threadIdx.x; i < head; i += blockDim.x) { const double v = (double)g[i]; gs += v; gss += v * v; }
+        for (int i = head + 4 * nv + threadIdx.x; i < n; i += blockDim.x) { const double v = (double)g[i]; gs += v; gss += v * v; }
     }
     if (depth) {
         const float* d = depth + (size_t)b * npix;

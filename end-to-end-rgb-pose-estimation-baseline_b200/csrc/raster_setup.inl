@@ -38,6 +38,11 @@ __device__ __forceinline__ bool project_vertex(const CamPose& c, const float* __
     return true;
 }
 
+// First triangle to touch a tile appends it to the raster work list.
+__device__ __forceinline__ void mark_tile(WorkCtl* ctl, unsigned* flags, unsigned* worklist, unsigned id) {
+    if (flags[id] == 0u && atomicExch(&flags[id], 1u) == 0u) worklist[atomicAdd(&ctl->n_work, 1u)] = id;
+}
+
 // One CTA = kSetupThreads consecutive triangles of one image.  Survivors that touch at most 2x2 tiles are
 // binned: the CTA counts them per tile in shared memory, scans the counts, and publishes
 //   desc[b][tile][cta] = (offset << 16) | count      (offset into the CTA's private 1024-B ref region)
@@ -48,7 +53,8 @@ __global__ void __launch_bounds__(kSetupThreads)
 setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
              float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_tri,
-             int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs) {
+             int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs,
+             WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ worklist) {
     __shared__ unsigned s_cnt[kMaxBinTiles];
     __shared__ unsigned s_off[kMaxBinTiles];
     __shared__ unsigned s_warp[kSetupThreads / 32];
@@ -122,7 +128,11 @@ setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids
         unsigned base = 0;
         if (lane == leader) base = atomicAdd(&stats[b].nlarge, (unsigned)__popc(m));
         base = __shfl_sync(0xffffffffu, base, leader);
-        if (large) large_tri[(size_t)b * maxT + base + __popc(m & ((1u << lane) - 1u))] = (unsigned)t;
+        if (large) {
+            large_tri[(size_t)b * maxT + base + __popc(m & ((1u << lane) - 1u))] = (unsigned)t;
+            for (int ty = ty0; ty <= ty1; ++ty)
+                for (int tx = tx0; tx <= tx1; ++tx) mark_tile(ctl, flags, worklist, (unsigned)(b * tg.nt + ty * tg.ntx + tx));
+        }
     }
     if (!tg.binned) return;   // CTA-uniform
     __syncthreads();
@@ -145,7 +155,8 @@ setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids
     for (int i = i_lo; i < i_hi; ++i) {
         const unsigned c = s_cnt[i];
         s_off[i] = run;
-        dimg[(size_t)i * tg.ncta_max] = (run << 16) | c;    // offset < 1024, count <= 256
+        dimg[(size_t)i * tg.ncta_max] = (run << 16) | c;    // offset <= 1024, count <= 256
+        if (c) mark_tile(ctl, flags, worklist, (unsigned)(b * tg.nt + i));
         run += c;
     }
     __syncthreads();

@@ -29,7 +29,7 @@ struct ShadeCtx {
 
 __device__ __forceinline__ float clamp01(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
 __device__ __forceinline__ float srgb_to_linear(float c) {
-    return c <= 0.04045f ? c * (1.0f / 12.92f) : powf((c + 0.055f) * (1.0f / 1.055f), 2.4f);
+    return c <= 0.04045f ? c * (1.0f / 12.92f) : __powf((c + 0.055f) * (1.0f / 1.055f), 2.4f);
 }
 
 // bilinear fetch from one mip level with GL_REPEAT wrap; returns sRGB-encoded rgb in [0,1]
@@ -75,11 +75,11 @@ __device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __rest
     const int Pcx = px * kSubpix + 128, Pcy = py * kSubpix + 128;
     float iz = fmaf(g.gy, (float)(Pcy - g.Y0), fmaf(g.gx, (float)(Pcx - g.X0), g.iz0));
     iz = fminf(fmaxf(iz, sc.iz_min), sc.iz_max);
-    const float z = 1.0f / iz;
+    const float z = __fdividef(1.0f, iz);   // fast-math shading: colour parity bar is 2/255 (north_star), not bit-exactness
     const float x = ((px + 0.5f) - sc.cx) * sc.fx_inv * z;
     const float y = ((py + 0.5f) - sc.cy) * sc.fy_inv * z;
     const float dist2 = x * x + y * y + z * z;
-    const float inv_d = 1.0f / sqrtf(dist2);
+    const float inv_d = rsqrtf(dist2);
     // camera and light sit at the origin: l = v = h = -p/|p|
     const float ndl = -(nx * x + ny * y + nz * z) * inv_d;
     const float nl = fminf(fmaxf(ndl, 0.001f), 1.0f);
@@ -88,7 +88,7 @@ __device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __rest
     // spot cone around the camera's forward axis (+z in the OpenCV frame)
     const float cd = clamp01(z * inv_d);
     float att = clamp01(cd * sc.las + sc.lao);
-    att = att * att / dist2;
+    att = att * att * (inv_d * inv_d);
     const float radiance = att * sc.intensity;
 
     float base[3] = {sc.base[0], sc.base[1], sc.base[2]};
@@ -139,10 +139,10 @@ __device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __rest
 
     // metallic-roughness BRDF with v = l = h: vh = 1 -> Fresnel = f0
     const float kk = sc.kgeo;
-    const float G = (nl / (nl * (1.0f - kk) + kk)) * (nv / (nv * (1.0f - kk) + kk));
+    const float G = __fdividef(nl, nl * (1.0f - kk) + kk) * __fdividef(nv, nv * (1.0f - kk) + kk);
     const float dd = nh * nh * (sc.alpha2 - 1.0f) + 1.0f;
-    const float D = sc.alpha2 / (3.14159265358979f * dd * dd);
-    const float spec_common = G * D / (4.0f * nl * nv + 1e-4f);
+    const float D = __fdividef(sc.alpha2, 3.14159265358979f * dd * dd);
+    const float spec_common = __fdividef(G * D, 4.0f * nl * nv + 1e-4f);
     unsigned out = 0xFF000000u;
     // untextured default material: r = g = b, one gamma evaluation serves all three channels
     const bool gray = (base[0] == base[1]) && (base[1] == base[2]);
@@ -154,7 +154,7 @@ __device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __rest
         const float cdiff = base[c] * 0.96f * (1.0f - sc.metallic);
         const float diffuse = (1.0f - f0) * cdiff * (1.0f / 3.14159265358979f);
         const float col = nl * radiance * (diffuse + f0 * spec_common) + base[c] * sc.ambient;
-        const float enc = clamp01(powf(fmaxf(col, 0.0f), 1.0f / 2.2f));
+        const float enc = clamp01(__powf(fmaxf(col, 0.0f), 1.0f / 2.2f));
         const unsigned q = (unsigned)(enc * 255.0f + 0.5f);
         if (c == 0) qfirst = q;
         out |= q << (8 * c);

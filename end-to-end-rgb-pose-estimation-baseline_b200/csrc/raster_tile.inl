@@ -107,14 +107,124 @@ __device__ __forceinline__ void process_queue(const int* queue, int qn, int* med
     __syncthreads();
 }
 
+// Binned triangles (int32-exact), flattened so that lanes stay busy: each thread stages one queued triangle
+// (edge equations relative to its clipped bbox origin, depth plane, id) in shared memory and lists the bbox
+// pixels it must visit; the warp then walks the concatenated (triangle, pixel) items of its 32 triangles, 32 per
+// step, so a 1-pixel triangle and a 16-pixel triangle in the same warp cost 17 items, not 2 x 16.
+// Triangles with more than kSmallPix bbox pixels take the warp-per-triangle path.
+constexpr int kTriStride = 20;   // words per staged triangle (16 used; 80 B keeps LDS.128 aligned and conflict-free)
+
+constexpr size_t kRasterSmemBytes = (size_t)kTilePix * 32 + sizeof(int) * 2 * kQueueCap +
+                                    sizeof(int) * kRasterThreads * kTriStride + sizeof(unsigned short) * kRasterThreads * kSmallPix;
+
+__device__ __forceinline__ void process_queue_flat(const int* queue, int qn, int* medq, int* med_count,
+                                                   const int4* __restrict__ img_recs, unsigned long long* keys,
+                                                   int* s_tri, unsigned short* s_items,
+                                                   int x_lo, int x_hi, int y_lo, int y_hi, float c0, float c1) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int SX[4] = {96, 224, 32, 160};
+    constexpr int SY[4] = {32, 96, 160, 224};
+    unsigned short* items = s_items + warp * (32 * kSmallPix);
+    for (int qb = 0; qb < qn; qb += kRasterThreads) {
+        const int k = qb + tid;
+        int n = 0, w = 0, h = 0;
+        if (k < qn) {
+            const unsigned tri = (unsigned)queue[k];
+            const int4* r = img_recs + 3 * (size_t)tri;
+            const int4 q0 = r[0], q1 = r[1], q2 = r[2];
+            const TriGeom g = unpack_geom(q0, q1, q2);
+            int bx0, bx1, by0, by1;
+            tri_bbox(g, x_lo, x_hi, y_lo, y_hi, bx0, bx1, by0, by1);
+            if (bx0 <= bx1 && by0 <= by1) {
+                w = bx1 - bx0 + 1; h = by1 - by0 + 1;
+                if (w * h <= kSmallPix) {
+                    n = w * h;
+                    const int dx0 = g.X1 - g.X0, dy0 = g.Y1 - g.Y0;
+                    const int dx1 = g.X2 - g.X1, dy1 = g.Y2 - g.Y1;
+                    const int dx2 = g.X0 - g.X2, dy2 = g.Y0 - g.Y2;
+                    const int b0 = (dy0 < 0 || (dy0 == 0 && dx0 > 0)) ? 0 : -1;
+                    const int b1 = (dy1 < 0 || (dy1 == 0 && dx1 > 0)) ? 0 : -1;
+                    const int b2 = (dy2 < 0 || (dy2 == 0 && dx2 > 0)) ? 0 : -1;
+                    const int ox = bx0 * kSubpix, oy = by0 * kSubpix;
+                    int4* slot = reinterpret_cast<int4*>(s_tri + tid * kTriStride);
+                    const int C0 = dx0 * (oy - g.Y0) - dy0 * (ox - g.X0) + b0;
+                    const int C1 = dx1 * (oy - g.Y1) - dy1 * (ox - g.X1) + b1;
+                    const int C2 = dx2 * (oy - g.Y2) - dy2 * (ox - g.X2) + b2;
+                    slot[0] = make_int4(-dy0, dx0, C0, -dy1);
+                    slot[1] = make_int4(dx1, C1, -dy2, dx2);
+                    slot[2] = make_int4(C2, ox - g.X0, oy - g.Y0, __float_as_int(g.gx));
+                    slot[3] = make_int4(__float_as_int(g.gy), __float_as_int(g.iz0), (int)tri,
+                                        (by0 - y_lo) * kTile + (bx0 - x_lo));
+                } else {
+                    medq[atomicAdd(med_count, 1)] = (int)tri;
+                }
+            }
+        }
+        int incl = n;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        const int total = __shfl_sync(0xffffffffu, incl, 31);
+        if (n) {
+            int idx = incl - n;
+            for (int dy = 0; dy < h; ++dy)
+                for (int dx = 0; dx < w; ++dx) items[idx++] = (unsigned short)(lane | (dx << 5) | (dy << 9));
+        }
+        __syncwarp();
+        for (int j = lane; j < total; j += 32) {
+            const int code = items[j];
+            const int dxp = (code >> 5) & 15, dyp = code >> 9;
+            const int4* slot = reinterpret_cast<const int4*>(s_tri + ((warp << 5) + (code & 31)) * kTriStride);
+            const int4 a = slot[0], b = slot[1], c = slot[2], d = slot[3];
+            const int sx = dxp * kSubpix, sy = dyp * kSubpix;
+            const float gx = __int_as_float(c.w), gy = __int_as_float(d.x), iz0 = __int_as_float(d.y);
+            const int pidx = d.w + dyp * kTile + dxp;
+#pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                const int ux = sx + SX[s], uy = sy + SY[s];
+                const int e0 = a.z + a.x * ux + a.y * uy;
+                const int e1 = b.y + a.w * ux + b.x * uy;
+                const int e2 = c.x + b.z * ux + b.w * uy;
+                if ((e0 | e1 | e2) >= 0) {
+                    const float fxr = (float)(c.y + ux), fyr = (float)(c.z + uy);
+                    const float iz = __fmaf_rn(gy, fyr, __fmaf_rn(gx, fxr, iz0));
+                    const float dd = __fmaf_rn(-c1, iz, c0);
+                    if (dd >= 0.0f && dd <= 1.0f) {
+                        const unsigned d24 = (unsigned)__float2int_rn(__fmul_rn(dd, 16777215.0f));
+                        if (d24 < kDepthMax)
+                            smem_min64(&keys[s * kTilePix + pidx], ((unsigned long long)d24 << 32) | (unsigned)d.z);
+                    }
+                }
+            }
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    const int mn = *med_count;
+    for (int k = warp; k < mn; k += kRasterThreads / 32) {
+        const unsigned tri = (unsigned)medq[k];
+        const int4* r = img_recs + 3 * (size_t)tri;
+        const TriGeom g = unpack_geom(r[0], r[1], r[2]);
+        int bx0, bx1, by0, by1;
+        tri_bbox(g, x_lo, x_hi, y_lo, y_hi, bx0, bx1, by0, by1);
+        raster_tri<int>(g, tri, bx0, bx1, by0, by1, lane, 32, keys, x_lo, y_lo, c0, c1);
+    }
+    __syncthreads();
+    if (tid == 0) *med_count = 0;
+    __syncthreads();
+}
+
 struct TileAcc {
     unsigned qmax, dcount;
     float dmax;
-    double dsum, dsumsq, gsum, gsumsq;
+    double dsum, dsumsq;
 };
 
 // Everything one CTA does for tile `tile` of image `b`: gather -> coverage/depth -> shade/resolve -> RGBA8 + depth
-// stores -> per-image accumulators.  smem_raw: keys [4][kTilePix] u64, queue [kQueueCap], medq [kQueueCap].
+// stores -> per-image accumulators.  smem_raw: keys [4][kTilePix] u64, queue [kQueueCap], medq [kQueueCap],
+// staged triangles [kRasterThreads][kTriStride], item lists [8][32*kSmallPix] u16.
 __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl, unsigned* s_scan,
                                             const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids,
                                             int uniform_mesh, const float* __restrict__ T_CO, const float* __restrict__ K,
@@ -122,11 +232,12 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
                                             ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
                                             const int4* __restrict__ recs, const unsigned* __restrict__ desc,
                                             const unsigned char* __restrict__ refs, unsigned* __restrict__ rgba_out,
-                                            float* __restrict__ depth_out, const float* __restrict__ gt_hwc,
-                                            int b, int tile) {
+                                            float* __restrict__ depth_out, int b, int tile) {
     unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw);           // [4][kTilePix]
     int* queue = reinterpret_cast<int*>(keys + 4 * kTilePix);                              // [kQueueCap]
     int* medq = queue + kQueueCap;                                                         // [kQueueCap]
+    int* s_tri = medq + kQueueCap;                                                         // [kRasterThreads][kTriStride]
+    unsigned short* s_items = reinterpret_cast<unsigned short*>(s_tri + kRasterThreads * kTriStride);  // [8][32*kSmallPix]
     int* q_count = s_ctl, *med_count = s_ctl + 1;
     unsigned* s_dcnt = s_scan;                      // [kRasterThreads] descriptor counts
     unsigned* s_dscan = s_scan + kRasterThreads;    // [kRasterThreads] exclusive scan
@@ -187,7 +298,7 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
             }
             __syncthreads();
             const int qn = (int)min((unsigned)kQueueCap, total - base);
-            process_queue<int>(queue, qn, medq, med_count, img_recs, keys, x_lo, x_hi, y_lo, y_hi, S.c0, S.c1);
+            process_queue_flat(queue, qn, medq, med_count, img_recs, keys, s_tri, s_items, x_lo, x_hi, y_lo, y_hi, S.c0, S.c1);
         }
     }
 
@@ -222,7 +333,7 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
     // ---- resolve + shade + write, and per-image accumulators ----
     const int tw = x_hi - x_lo + 1, th = y_hi - y_lo + 1;
     TileAcc acc;
-    acc.qmax = 0; acc.dcount = 0; acc.dmax = 0.0f; acc.dsum = 0.0; acc.dsumsq = 0.0; acc.gsum = 0.0; acc.gsumsq = 0.0;
+    acc.qmax = 0; acc.dcount = 0; acc.dmax = 0.0f; acc.dsum = 0.0; acc.dsumsq = 0.0;
     const size_t img_pix = (size_t)b * W * H;
     if (!inited) {
         for (int p = tid; p < kTilePix; p += kRasterThreads) {
@@ -270,52 +381,54 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
             if (depth > 0.01f) { acc.dcount++; acc.dsum += (double)depth; acc.dsumsq += (double)depth * (double)depth; }
         }
     }
-    if (gt_hwc) {
-        // this tile's share of the gt crop statistics (normalize_img, data_loaders.py:79-82): rows of 3*tw floats
-        const int rowf = 3 * tw;
-        for (int i = tid; i < rowf * th; i += kRasterThreads) {
-            const int ly = i / rowf, c = i - ly * rowf;
-            const double v = (double)__ldg(gt_hwc + 3 * (img_pix + (size_t)(y_lo + ly) * W + x_lo) + c);
-            acc.gsum += v; acc.gsumsq += v * v;
-        }
-    }
     // block reduction -> one atomic per accumulator per CTA
-    __shared__ double red_d[4][kRasterThreads / 32];
+    __shared__ double red_d[2][kRasterThreads / 32];
     __shared__ unsigned red_u[3][kRasterThreads / 32];
     acc.qmax = warp_max(acc.qmax);
     acc.dcount = (unsigned)__reduce_add_sync(0xffffffffu, acc.dcount);
     const unsigned dmax_bits = warp_max(__float_as_uint(acc.dmax));
     acc.dsum = warp_sum(acc.dsum); acc.dsumsq = warp_sum(acc.dsumsq);
-    acc.gsum = warp_sum(acc.gsum); acc.gsumsq = warp_sum(acc.gsumsq);
     if (lane == 0) {
         red_u[0][warp] = acc.qmax; red_u[1][warp] = acc.dcount; red_u[2][warp] = dmax_bits;
-        red_d[0][warp] = acc.dsum; red_d[1][warp] = acc.dsumsq; red_d[2][warp] = acc.gsum; red_d[3][warp] = acc.gsumsq;
+        red_d[0][warp] = acc.dsum; red_d[1][warp] = acc.dsumsq;
     }
     __syncthreads();
     if (tid == 0) {
         unsigned qm = 0, dc = 0, dm = 0;
-        double a = 0, c = 0, e = 0, f = 0;
+        double a = 0, c = 0;
         for (int w = 0; w < kRasterThreads / 32; ++w) {
             qm = max(qm, red_u[0][w]); dc += red_u[1][w]; dm = max(dm, red_u[2][w]);
-            a += red_d[0][w]; c += red_d[1][w]; e += red_d[2][w]; f += red_d[3][w];
+            a += red_d[0][w]; c += red_d[1][w];
         }
         ImgStats* st = stats + b;
         if (qm) atomicMax(&st->qmax, qm);
         if (dc) { atomicAdd(&st->dcount, dc); atomicAdd(&st->dsum, a); atomicAdd(&st->dsumsq, c); }
         if (dm) atomicMax(&st->dmax_bits, dm);
-        if (gt_hwc) { atomicAdd(&st->gsum, e); atomicAdd(&st->gsumsq, f); }
     }
 }
 
-__global__ void __launch_bounds__(kRasterThreads)
+// Persistent CTAs pop non-empty tiles from the work list setup_kernel built (empty tiles are never visited:
+// the finalize kernels treat a zero flag as background).
+__global__ void __launch_bounds__(kRasterThreads, 3)
 raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
               const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
               SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
               const int4* __restrict__ recs, const unsigned* __restrict__ desc, const unsigned char* __restrict__ refs,
-              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, const float* __restrict__ gt_hwc) {
+              WorkCtl* __restrict__ ctl, const unsigned* __restrict__ worklist,
+              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_ctl[2];
+    __shared__ unsigned s_item;
     __shared__ unsigned s_scan[3 * kRasterThreads + kRasterThreads / 32];
-    raster_tile(smem_raw, s_ctl, s_scan, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_tri,
-                recs, desc, refs, rgba_out, depth_out, gt_hwc, blockIdx.y, blockIdx.x);
+    const unsigned n_work = ctl->n_work;    // final: written by setup_kernel (previous launch)
+    for (;;) {
+        if (threadIdx.x == 0) s_item = atomicAdd(&ctl->next, 1u);
+        __syncthreads();
+        const unsigned item = s_item;
+        if (item >= n_work) break;
+        const unsigned id = worklist[item];
+        raster_tile(smem_raw, s_ctl, s_scan, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_tri,
+                    recs, desc, refs, rgba_out, depth_out, (int)(id / (unsigned)tg.nt), (int)(id % (unsigned)tg.nt));
+        __syncthreads();
+    }
 }
