@@ -345,36 +345,86 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
             }
         }
     } else {
+        // Flattened shading.  R1: every pixel finds the distinct triangles among its 4 samples and lists one
+        // (pixel, sample) item per distinct triangle; R2: the items are shaded 256 at a time (no lane idles on
+        // background or waits for a neighbour's 4-triangle edge pixel) and the RGBA8 colour replaces the triangle
+        // id in the key's low word; R3: every pixel sums its samples' colours through the representatives.
         const CamPose cam = load_campose(T_CO, K, b);
         const ShadeCtx sc = make_shade_ctx(mesh, cam, S);
-        for (int p = tid; p < kTilePix; p += kRasterThreads) {
+        unsigned short* sitems = reinterpret_cast<unsigned short*>(queue);   // [4 * kTilePix] aliases queue + medq
+        unsigned* key_lo = reinterpret_cast<unsigned*>(keys);
+        constexpr int kPer = kTilePix / kRasterThreads;
+        unsigned info[kPer];     // per pixel: rep[s] (2 bits each) | covered mask << 8
+        unsigned d24s[kPer];     // depth of sample 0
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) {
+            const int p = tid + i * kRasterThreads;
             const int lx = p & (kTile - 1), ly = p / kTile;
-            if (lx >= tw || ly >= th) continue;
-            const int px = x_lo + lx, py = y_lo + ly;
             unsigned long long k[4];
 #pragma unroll
-            for (int s = 0; s < 4; ++s) k[s] = keys[s * kTilePix + p];
-            unsigned col[4];
+            for (int sidx = 0; sidx < 4; ++sidx)
+                k[sidx] = (lx < tw && ly < th) ? keys[sidx * kTilePix + p] : kKeyEmpty;
+            unsigned reps = 0, mask = 0, fresh = 0;
+#pragma unroll
+            for (int sidx = 0; sidx < 4; ++sidx) {
+                if (k[sidx] != kKeyEmpty) {
+                    mask |= 1u << sidx;
+                    unsigned rep = sidx;
+#pragma unroll
+                    for (int j = sidx - 1; j >= 0; --j)
+                        if (k[j] != kKeyEmpty && (unsigned)k[j] == (unsigned)k[sidx]) rep = j;
+                    reps |= rep << (2 * sidx);
+                    if (rep == (unsigned)sidx) fresh |= 1u << sidx;
+                }
+            }
+            info[i] = reps | (mask << 8);
+            d24s[i] = (mask & 1u) ? (unsigned)(k[0] >> 32) : kDepthMax;
+            // append this pixel's items (warp-aggregated)
+            const int c = __popc(fresh);
+            int incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            int base = 0;
+            if (lane == 31 && incl) base = atomicAdd(q_count, incl);
+            base = __shfl_sync(0xffffffffu, base, 31) + incl - c;
+#pragma unroll
+            for (int sidx = 0; sidx < 4; ++sidx)
+                if (fresh & (1u << sidx)) sitems[base++] = (unsigned short)(p | (sidx << 10));
+        }
+        __syncthreads();
+        const int nitems = *q_count;
+        for (int it = tid; it < nitems; it += kRasterThreads) {
+            const int code = sitems[it];
+            const int p = code & (kTilePix - 1), sidx = code >> 10;
+            const unsigned tri = key_lo[2 * (sidx * kTilePix + p)];
+            key_lo[2 * (sidx * kTilePix + p)] = shade(sc, img_recs + 3 * (size_t)tri, tri, x_lo + (p & (kTile - 1)), y_lo + p / kTile);
+        }
+        __syncthreads();
+        if (tid == 0) *q_count = 0;
+#pragma unroll
+        for (int i = 0; i < kPer; ++i) {
+            const int p = tid + i * kRasterThreads;
+            const int lx = p & (kTile - 1), ly = p / kTile;
+            if (lx >= tw || ly >= th) continue;
+            const unsigned mask = info[i] >> 8;
             unsigned sum_r = 0, sum_g = 0, sum_b = 0, sum_a = 0;
 #pragma unroll
-            for (int s = 0; s < 4; ++s) {
-                col[s] = 0u;
-                if (k[s] != kKeyEmpty) {
-                    const unsigned tri = (unsigned)k[s];
-                    bool found = false;
-#pragma unroll
-                    for (int j = 0; j < s; ++j)
-                        if (!found && k[j] != kKeyEmpty && (unsigned)k[j] == tri) { col[s] = col[j]; found = true; }
-                    if (!found) col[s] = shade(sc, img_recs + 3 * (size_t)tri, tri, px, py);
-                    sum_r += col[s] & 0xFFu; sum_g += (col[s] >> 8) & 0xFFu;
-                    sum_b += (col[s] >> 16) & 0xFFu; sum_a += col[s] >> 24;
+            for (int sidx = 0; sidx < 4; ++sidx) {
+                if (mask & (1u << sidx)) {
+                    const unsigned rep = (info[i] >> (2 * sidx)) & 3u;
+                    const unsigned col = key_lo[2 * (rep * kTilePix + p)];
+                    sum_r += col & 0xFFu; sum_g += (col >> 8) & 0xFFu;
+                    sum_b += (col >> 16) & 0xFFu; sum_a += col >> 24;
                 }
             }
             const unsigned r8 = (sum_r + 2u) >> 2, g8 = (sum_g + 2u) >> 2, b8 = (sum_b + 2u) >> 2, a8 = (sum_a + 2u) >> 2;
-            const size_t o = img_pix + (size_t)py * W + px;
+            const size_t o = img_pix + (size_t)(y_lo + ly) * W + (x_lo + lx);
             rgba_out[o] = r8 | (g8 << 8) | (b8 << 16) | (a8 << 24);
             float depth = 0.0f;
-            if (k[0] != kKeyEmpty) depth = depth_readback((unsigned)(k[0] >> 32), S);
+            if (mask & 1u) depth = depth_readback(d24s[i], S);
             depth_out[o] = depth;
             acc.qmax = max(acc.qmax, max(r8, max(g8, b8)));
             acc.dmax = fmaxf(acc.dmax, depth);
