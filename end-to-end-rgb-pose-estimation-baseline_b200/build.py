@@ -15,7 +15,8 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librac_b200.so")
 STAMP = os.path.join(HERE, ".librac_b200.stamp")
 SOURCES = ["rac_api.cu", "raster.cu", "pose_update.cu", "add_loss.cu"]
-HEADERS = ["rac_common.cuh", "raster.cuh", os.path.join("..", "..", "include", "rac.h")]
+HEADERS = ["rac_common.cuh", "raster.cuh", "raster_setup.inl", "raster_shade.inl", "raster_tile.inl", "raster_finalize.inl",
+           os.path.join("..", "..", "include", "rac.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -39,6 +40,18 @@ def _digest():
             h.update(f.read())
     h.update(" ".join(NVCC_FLAGS).encode())
     return h.hexdigest()
+
+
+def build_variant(out_path, extra_flags, verbose=False):
+    """Diagnostic builds (e.g. -DRAC_PHASE_TIMING for profiles/phase_timing.py); never the product library."""
+    cmd = [_nvcc()] + NVCC_FLAGS + list(extra_flags) + (["-Xptxas", "-v"] if verbose else [])
+    cmd += [os.path.join(CSRC, s) for s in SOURCES] + ["-o", out_path]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        sys.stderr.write(res.stdout + res.stderr)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed building " + out_path)
+    return out_path
 
 
 def build(force=False, verbose=False):

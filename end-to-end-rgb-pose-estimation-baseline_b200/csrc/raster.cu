@@ -6,11 +6,11 @@
 // Three kernels per call (see raster.cuh for the spec they implement):
 //   setup_kernel     (raster_setup.inl) one thread per (image, triangle): transform, project, snap, cull,
 //                    1/z plane, camera-frame normal -> TriRec.  The CTA (256 triangles of one image) bins
-//                    its survivors by 32x32-px tile in shared memory and publishes, without any global
+//                    its survivors by 32x16-px tile in shared memory and publishes, without any global
 //                    atomic, a private ref region (u8 local ids grouped by tile) plus one descriptor per
 //                    tile.  Triangles spanning more than 2x2 tiles go to a per-image large list.
 //   raster_kernel    (raster_tile.inl, raster_shade.inl) one CTA per (image, tile): the tile's 4x-MSAA
-//                    visibility buffer (depth24 | triangle id, 8 B per sample, 32 KB) lives in shared
+//                    visibility buffer (depth24 | triangle id, 8 B per sample, 16 KB) lives in shared
 //                    memory; the tile's triangles are gathered through the descriptors and scattered into
 //                    it with shared-memory atomic-min (exact int32 edge functions for binned triangles,
 //                    int64 for large ones); then every pixel is shaded + resolved once and written as
@@ -36,8 +36,8 @@ static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 static TileGrid make_tile_grid(int W, int H, int maxT) {
     TileGrid tg;
-    tg.ntx = (W + kTile - 1) / kTile;
-    tg.nty = (H + kTile - 1) / kTile;
+    tg.ntx = (W + kTileW - 1) / kTileW;
+    tg.nty = (H + kTileH - 1) / kTileH;
     tg.nt = tg.ntx * tg.nty;
     tg.binned = tg.nt <= kMaxBinTiles ? 1 : 0;
     tg.ncta_max = (maxT + kSetupThreads - 1) / kSetupThreads;
@@ -102,6 +102,17 @@ static int g_stage_next = 0;
 
 static int upload_ids(const int32_t* h_ids, int B, int* d_dst, cudaStream_t stream) {
     std::lock_guard<std::mutex> lk(g_stage_mu);
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    RAC_CUDA_CHECK(cudaStreamIsCapturing(stream, &cap));
+    if (cap != cudaStreamCaptureStatusNone) {
+        // graph capture: the memcpy node keeps the source pointer, so it gets a buffer of its own that is never
+        // reused (B ints per captured call, lives as long as the process)
+        int* h = nullptr;
+        RAC_CUDA_CHECK(cudaMallocHost(&h, sizeof(int) * (size_t)B));
+        for (int i = 0; i < B; ++i) h[i] = h_ids[i];
+        RAC_CUDA_CHECK(cudaMemcpyAsync(d_dst, h, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice, stream));
+        return RAC_OK;
+    }
     IdStage& st = g_stage[g_stage_next];
     g_stage_next = (g_stage_next + 1) % 8;
     if (st.pending) { RAC_CUDA_CHECK(cudaEventSynchronize(st.ev)); st.pending = false; }

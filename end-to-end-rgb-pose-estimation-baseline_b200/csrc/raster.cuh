@@ -26,7 +26,8 @@ constexpr int kSubpix = 256;          // 8 subpixel bits
 constexpr float kGuardPx = 16384.0f;  // guard band in pixels
 constexpr unsigned kDepthMax = 0xFFFFFFu;
 constexpr unsigned long long kKeyEmpty = ~0ull;
-constexpr int kTile = 32;             // raster tile edge in pixels (visibility buffer: 32*32*4 samples*8 B = 32 KB)
+constexpr int kTileW = 32;            // raster tile in pixels: 32 x 16 (visibility buffer: 512 px * 4 samples * 8 B = 16 KB);
+constexpr int kTileH = 16;            // 32 px wide keeps every output row segment one 128-B line
 constexpr int kSetupThreads = 256;    // triangles per setup CTA (= refs per descriptor, u8 local ids)
 constexpr int kMaxBinTiles = 2048;    // images with more tiles (> 2 Mpx) skip binning: every triangle is "large"
 

@@ -60,7 +60,7 @@ struct FlagView {
 __device__ __forceinline__ bool pixel_live(const FlagView& fv, int b, int p) {
     if (!fv.flags) return true;
     const int y = p / fv.W, x = p - y * fv.W;
-    return fv.flags[(size_t)b * fv.nt + (y / kTile) * fv.ntx + (x / kTile)] != 0u;
+    return fv.flags[(size_t)b * fv.nt + (y / kTileH) * fv.ntx + (x / kTileW)] != 0u;
 }
 
 // One thread = 4 consecutive pixels of one image (requires W*H % 4 == 0 and 16-B aligned planes).

@@ -90,7 +90,7 @@ setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids
         const int px0 = max(ceil_div256(xmin - 224), 0), px1 = min(floor_div256(xmax - 32), W - 1);
         const int py0 = max(ceil_div256(ymin - 224), 0), py1 = min(floor_div256(ymax - 32), H - 1);
         keep = (px0 <= px1) && (py0 <= py1);
-        tx0 = px0 / kTile; tx1 = px1 / kTile; ty0 = py0 / kTile; ty1 = py1 / kTile;
+        tx0 = px0 / kTileW; tx1 = px1 / kTileW; ty0 = py0 / kTileH; ty1 = py1 / kTileH;
     }
     if (keep) {
         // swap v1 <-> v2 so that the interior is on the non-negative side of all three edges

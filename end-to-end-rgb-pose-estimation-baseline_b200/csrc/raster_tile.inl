@@ -1,10 +1,29 @@
-// raster_tile.inl — raster_kernel: one CTA per (image, 32x32-px tile).  Spec: RS-C, RS-Z, RS-R in raster.cuh.
+// raster_tile.inl — raster_kernel: one CTA per (image, 32x16-px tile) work item.  Spec: RS-C, RS-Z, RS-R in raster.cuh.
 // Included by raster.cu (inside namespace rac).
+
+// Optional phase timeline (build with -DRAC_PHASE_TIMING): thread 0 of every CTA accumulates clock64() deltas per
+// phase into WorkCtl::pad (read back from the workspace by profiles/phase_timing.py).  Off in the product build.
+#ifdef RAC_PHASE_TIMING
+#define RAC_PHASE(idx)                                                                                          \
+    do {                                                                                                        \
+        if (threadIdx.x == 0) {                                                                                 \
+            const long long _t = clock64();                                                                     \
+            atomicAdd(reinterpret_cast<unsigned long long*>(g_phase_ctl->pad) + (idx), (unsigned long long)(_t - g_phase_t)); \
+            g_phase_t = _t;                                                                                     \
+        }                                                                                                       \
+    } while (0)
+#define RAC_PHASE_ARGS , WorkCtl* g_phase_ctl, long long& g_phase_t
+#define RAC_PHASE_PASS , g_phase_ctl, g_phase_t
+#else
+#define RAC_PHASE(idx) do { } while (0)
+#define RAC_PHASE_ARGS
+#define RAC_PHASE_PASS
+#endif
 
 constexpr int kRasterThreads = 256;
 constexpr int kQueueCap = 1024;       // triangle queue per flush
 constexpr int kSmallPix = 16;         // bbox∩tile pixels handled by one thread; larger -> one warp
-constexpr int kTilePix = kTile * kTile;
+constexpr int kTilePix = kTileW * kTileH;
 
 __device__ __forceinline__ void smem_min64(unsigned long long* addr, unsigned long long v) {
     unsigned long long old = *(volatile unsigned long long*)addr;
@@ -52,7 +71,7 @@ __device__ __forceinline__ void raster_tri(const TriGeom& g, unsigned tri, int b
         const I E0 = dx0 * (I)(oy - g.Y0) - dy0 * (I)(ox - g.X0) + b0;
         const I E1 = dx1 * (I)(oy - g.Y1) - dy1 * (I)(ox - g.X1) + b1;
         const I E2 = dx2 * (I)(oy - g.Y2) - dy2 * (I)(ox - g.X2) + b2;
-        const int pidx = (py - tile_y0) * kTile + (px - tile_x0);
+        const int pidx = (py - tile_y0) * kTileW + (px - tile_x0);
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
             const I e0 = E0 + dx0 * (I)SY[s] - dy0 * (I)SX[s];
@@ -120,7 +139,8 @@ constexpr size_t kRasterSmemBytes = (size_t)kTilePix * 32 + sizeof(int) * 2 * kQ
 __device__ __forceinline__ void process_queue_flat(const int* queue, int qn, int* medq, int* med_count,
                                                    const int4* __restrict__ img_recs, unsigned long long* keys,
                                                    int* s_tri, unsigned short* s_items,
-                                                   int x_lo, int x_hi, int y_lo, int y_hi, float c0, float c1) {
+                                                   int x_lo, int x_hi, int y_lo, int y_hi, float c0, float c1
+                                                   RAC_PHASE_ARGS) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int SX[4] = {96, 224, 32, 160};
     constexpr int SY[4] = {32, 96, 160, 224};
@@ -154,7 +174,7 @@ __device__ __forceinline__ void process_queue_flat(const int* queue, int qn, int
                     slot[1] = make_int4(dx1, C1, -dy2, dx2);
                     slot[2] = make_int4(C2, ox - g.X0, oy - g.Y0, __float_as_int(g.gx));
                     slot[3] = make_int4(__float_as_int(g.gy), __float_as_int(g.iz0), (int)tri,
-                                        (by0 - y_lo) * kTile + (bx0 - x_lo));
+                                        (by0 - y_lo) * kTileW + (bx0 - x_lo));
                 } else {
                     medq[atomicAdd(med_count, 1)] = (int)tri;
                 }
@@ -180,7 +200,7 @@ __device__ __forceinline__ void process_queue_flat(const int* queue, int qn, int
             const int4 a = slot[0], b = slot[1], c = slot[2], d = slot[3];
             const int sx = dxp * kSubpix, sy = dyp * kSubpix;
             const float gx = __int_as_float(c.w), gy = __int_as_float(d.x), iz0 = __int_as_float(d.y);
-            const int pidx = d.w + dyp * kTile + dxp;
+            const int pidx = d.w + dyp * kTileW + dxp;
 #pragma unroll
             for (int s = 0; s < 4; ++s) {
                 const int ux = sx + SX[s], uy = sy + SY[s];
@@ -201,7 +221,9 @@ __device__ __forceinline__ void process_queue_flat(const int* queue, int qn, int
         }
         __syncwarp();
     }
+    RAC_PHASE(2);
     __syncthreads();
+    RAC_PHASE(3);
     const int mn = *med_count;
     for (int k = warp; k < mn; k += kRasterThreads / 32) {
         const unsigned tri = (unsigned)medq[k];
@@ -212,6 +234,7 @@ __device__ __forceinline__ void process_queue_flat(const int* queue, int qn, int
         raster_tri<int>(g, tri, bx0, bx1, by0, by1, lane, 32, keys, x_lo, y_lo, c0, c1);
     }
     __syncthreads();
+    RAC_PHASE(4);
     if (tid == 0) *med_count = 0;
     __syncthreads();
 }
@@ -232,7 +255,7 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
                                             ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
                                             const int4* __restrict__ recs, const unsigned* __restrict__ desc,
                                             const unsigned char* __restrict__ refs, unsigned* __restrict__ rgba_out,
-                                            float* __restrict__ depth_out, int b, int tile) {
+                                            float* __restrict__ depth_out, int b, int tile RAC_PHASE_ARGS) {
     unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw);           // [4][kTilePix]
     int* queue = reinterpret_cast<int*>(keys + 4 * kTilePix);                              // [kQueueCap]
     int* medq = queue + kQueueCap;                                                         // [kQueueCap]
@@ -246,8 +269,8 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tx = tile % tg.ntx, ty = tile / tg.ntx;
-    const int x_lo = tx * kTile, y_lo = ty * kTile;
-    const int x_hi = min(x_lo + kTile, W) - 1, y_hi = min(y_lo + kTile, H) - 1;
+    const int x_lo = tx * kTileW, y_lo = ty * kTileH;
+    const int x_hi = min(x_lo + kTileW, W) - 1, y_hi = min(y_lo + kTileH, H) - 1;
     const MeshDev& mesh = table[mesh_ids ? mesh_ids[b] : uniform_mesh];
     const int4* img_recs = recs + 3 * (size_t)b * maxT;
     const unsigned n_large = stats[b].nlarge;   // written by setup_kernel (previous launch)
@@ -297,8 +320,9 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
                 inited = true;
             }
             __syncthreads();
+            RAC_PHASE(1);
             const int qn = (int)min((unsigned)kQueueCap, total - base);
-            process_queue_flat(queue, qn, medq, med_count, img_recs, keys, s_tri, s_items, x_lo, x_hi, y_lo, y_hi, S.c0, S.c1);
+            process_queue_flat(queue, qn, medq, med_count, img_recs, keys, s_tri, s_items, x_lo, x_hi, y_lo, y_hi, S.c0, S.c1 RAC_PHASE_PASS);
         }
     }
 
@@ -330,6 +354,7 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
         }
     }
 
+    RAC_PHASE(5);
     // ---- resolve + shade + write, and per-image accumulators ----
     const int tw = x_hi - x_lo + 1, th = y_hi - y_lo + 1;
     TileAcc acc;
@@ -337,7 +362,7 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
     const size_t img_pix = (size_t)b * W * H;
     if (!inited) {
         for (int p = tid; p < kTilePix; p += kRasterThreads) {
-            const int lx = p & (kTile - 1), ly = p / kTile;
+            const int lx = p & (kTileW - 1), ly = p / kTileW;
             if (lx < tw && ly < th) {
                 const size_t o = img_pix + (size_t)(y_lo + ly) * W + (x_lo + lx);
                 rgba_out[o] = 0u;
@@ -359,7 +384,7 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
 #pragma unroll
         for (int i = 0; i < kPer; ++i) {
             const int p = tid + i * kRasterThreads;
-            const int lx = p & (kTile - 1), ly = p / kTile;
+            const int lx = p & (kTileW - 1), ly = p / kTileW;
             unsigned long long k[4];
 #pragma unroll
             for (int sidx = 0; sidx < 4; ++sidx)
@@ -394,20 +419,24 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
             for (int sidx = 0; sidx < 4; ++sidx)
                 if (fresh & (1u << sidx)) sitems[base++] = (unsigned short)(p | (sidx << 10));
         }
+        RAC_PHASE(6);
         __syncthreads();
+        RAC_PHASE(7);
         const int nitems = *q_count;
         for (int it = tid; it < nitems; it += kRasterThreads) {
             const int code = sitems[it];
-            const int p = code & (kTilePix - 1), sidx = code >> 10;
+            const int p = code & 1023, sidx = code >> 10;
             const unsigned tri = key_lo[2 * (sidx * kTilePix + p)];
-            key_lo[2 * (sidx * kTilePix + p)] = shade(sc, img_recs + 3 * (size_t)tri, tri, x_lo + (p & (kTile - 1)), y_lo + p / kTile);
+            key_lo[2 * (sidx * kTilePix + p)] = shade(sc, img_recs + 3 * (size_t)tri, tri, x_lo + (p & (kTileW - 1)), y_lo + p / kTileW);
         }
+        RAC_PHASE(8);
         __syncthreads();
+        RAC_PHASE(9);
         if (tid == 0) *q_count = 0;
 #pragma unroll
         for (int i = 0; i < kPer; ++i) {
             const int p = tid + i * kRasterThreads;
-            const int lx = p & (kTile - 1), ly = p / kTile;
+            const int lx = p & (kTileW - 1), ly = p / kTileW;
             if (lx >= tw || ly >= th) continue;
             const unsigned mask = info[i] >> 8;
             unsigned sum_r = 0, sum_g = 0, sum_b = 0, sum_a = 0;
@@ -431,6 +460,7 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
             if (depth > 0.01f) { acc.dcount++; acc.dsum += (double)depth; acc.dsumsq += (double)depth * (double)depth; }
         }
     }
+    RAC_PHASE(10);
     // block reduction -> one atomic per accumulator per CTA
     __shared__ double red_d[2][kRasterThreads / 32];
     __shared__ unsigned red_u[3][kRasterThreads / 32];
@@ -459,7 +489,7 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
 
 // Persistent CTAs pop non-empty tiles from the work list setup_kernel built (empty tiles are never visited:
 // the finalize kernels treat a zero flag as background).
-__global__ void __launch_bounds__(kRasterThreads, 3)
+__global__ void __launch_bounds__(kRasterThreads, 4)
 raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
               const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
               SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
@@ -471,14 +501,21 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
     __shared__ unsigned s_item;
     __shared__ unsigned s_scan[3 * kRasterThreads + kRasterThreads / 32];
     const unsigned n_work = ctl->n_work;    // final: written by setup_kernel (previous launch)
+#ifdef RAC_PHASE_TIMING
+    WorkCtl* g_phase_ctl = ctl;
+    long long g_phase_t = clock64();
+#endif
     for (;;) {
         if (threadIdx.x == 0) s_item = atomicAdd(&ctl->next, 1u);
         __syncthreads();
         const unsigned item = s_item;
         if (item >= n_work) break;
         const unsigned id = worklist[item];
+        RAC_PHASE(0);
         raster_tile(smem_raw, s_ctl, s_scan, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_tri,
-                    recs, desc, refs, rgba_out, depth_out, (int)(id / (unsigned)tg.nt), (int)(id % (unsigned)tg.nt));
+                    recs, desc, refs, rgba_out, depth_out, (int)(id / (unsigned)tg.nt), (int)(id % (unsigned)tg.nt) RAC_PHASE_PASS);
+        RAC_PHASE(11);
         __syncthreads();
+        RAC_PHASE(12);
     }
 }

@@ -8,6 +8,7 @@ rac.mesh (load / procedural / device cache), rac.ops (autograd functions).
 from . import _lib, mesh, ops
 from ._lib import RacError, launch_count, lib
 from .render import assemble_input_device, render_batch_device, render_concat_device
+from .step import RenderCompareStep
 
 __all__ = ["_lib", "mesh", "ops", "RacError", "launch_count", "lib", "assemble_input_device",
-           "render_batch_device", "render_concat_device"]
+           "render_batch_device", "render_concat_device", "RenderCompareStep"]

@@ -6,7 +6,8 @@ import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _PKG = os.path.dirname(_HERE)
-LIB_PATH = os.path.join(_PKG, "librac_b200.so")
+# RAC_LIB selects a diagnostic build of the same sources (profiles/phase_timing.py); the default is the product library
+LIB_PATH = os.environ.get("RAC_LIB") or os.path.join(_PKG, "librac_b200.so")
 
 c_int = ctypes.c_int
 c_void_p = ctypes.c_void_p
