@@ -249,3 +249,18 @@ def test_full_size_properties(rac):
     dz = depth[v[ok], u[ok]]
     front = np.abs(dz - P[ok, 2]) < 0.01
     assert front.mean() > 0.1 and (dz[front] > 0).all()   # half the faces are dropped (holes) and half face away
+
+
+def test_committed_golden_vectors(rac):
+    """The CUDA path against the bytes committed in tests/golden/raster_golden.npz (oracle output generated by
+    tests/golden/make_raster_golden.py; the oracle source is not needed to run this check)."""
+    import make_raster_golden as G
+    gold = np.load(os.path.join(os.path.dirname(__file__), "golden", "raster_golden.npz"))
+    for name, (m, T, K) in G.scenes().items():
+        out = rac.render_batch_device(T, m, K, (G.W, G.H), want_rgba8=True)
+        rgba_o, depth_o = gold[f"{name}_rgba8"], gold[f"{name}_depth"]
+        qmax = np.float32(max(int(rgba_o[i, ..., :3].max()) for i in range(len(T))))
+        rgb_o = np.stack([rgba_o[i, ..., :3].astype(np.float32) / np.float32(max(int(rgba_o[i, ..., :3].max()), 1))
+                          for i in range(len(T))])
+        compare(out, (rgb_o, depth_o, rgba_o), G.W, G.H, "golden:" + name)
+        assert qmax > 0
