@@ -26,8 +26,8 @@ namespace rac {
 
 #include "raster_setup.inl"
 #include "raster_shade.inl"
-#include "raster_tile.inl"
 #include "raster_finalize.inl"
+#include "raster_tile.inl"
 
 // ---------------------------------------------------------------------------------------------
 // host side
@@ -44,6 +44,13 @@ static TileGrid make_tile_grid(int W, int H, int maxT) {
     return tg;
 }
 
+static FlagView make_flag_view(const unsigned* flags, int W, int H) {
+    const TileGrid tg = make_tile_grid(W, H, 1);
+    FlagView fv;
+    fv.flags = flags; fv.W = W; fv.ntx = tg.ntx; fv.nt = tg.nt;
+    return fv;
+}
+
 static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
     RenderWs w;
     char* p = (char*)base;
@@ -57,6 +64,7 @@ static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
     w.flags = (unsigned*)(p + off);          off = align256(off + sizeof(unsigned) * (size_t)B * tg.nt);
     w.zero_bytes = off;
     w.worklist = (unsigned*)(p + off);       off = align256(off + sizeof(unsigned) * (size_t)B * tg.nt);
+    w.img_base = (unsigned*)(p + off);       off = align256(off + sizeof(unsigned) * ((size_t)B + 1));
     w.mesh_ids = (int*)(p + off);            off = align256(off + sizeof(int) * (size_t)B);
     w.large_tri = (unsigned*)(p + off);      off = align256(off + sizeof(unsigned) * (size_t)B * maxT);
     w.recs = (int4*)(p + off);               off = align256(off + sizeof(int4) * 3 * (size_t)B * maxT);
@@ -130,9 +138,14 @@ static int upload_ids(const int32_t* h_ids, int B, int* d_dst, cudaStream_t stre
     return RAC_OK;
 }
 
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// `fin` arrives with the caller-facing fields set (mode, outputs, gt, use_norm_depth); the workspace-side fields are
+// filled here and the whole finalize pass runs as work items of raster_kernel.
 static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const float* d_K, int B, int W, int H,
-                         const rac_scene_t* scene, const float* d_gt_hwc, float* d_depth_user,
-                         void* d_ws, size_t ws_bytes, cudaStream_t stream, RenderWs* ws_out) {
+                         const rac_scene_t* scene, FinArgs fin, float* d_depth_user,
+                         void* d_ws, size_t ws_bytes, cudaStream_t stream) {
+    const float* d_gt_hwc = fin.gt_hwc;
     RAC_REQUIRE(h_mesh_ids && d_T_CO && d_K, "render: null mesh ids / T_CO / K");
     RAC_REQUIRE(B > 0 && W > 0 && H > 0, "render: B=%d W=%d H=%d must be positive", B, W, H);
     RAC_REQUIRE(W <= 8192 && H <= 8192, "render: image %dx%d exceeds the 8192 px limit", W, H);
@@ -177,7 +190,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         dim3 grid(tg.ncta_max, B);
         setup_kernel<<<grid, kSetupThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
                                                          ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs,
-                                                         ws.ctl, ws.flags, ws.worklist);
+                                                         ws.ctl, ws.flags, ws.worklist, ws.img_base, B);
         RAC_LAUNCHED();
     }
     {
@@ -196,22 +209,19 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
             RAC_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, raster_kernel, kRasterThreads, smem));
             if (ctas_per_sm < 1) ctas_per_sm = 1;
         }
-        const long long tiles = (long long)tg.nt * B;
-        const int grid = (int)(tiles < (long long)n_sm * ctas_per_sm ? tiles : (long long)n_sm * ctas_per_sm);
+        const int grid = n_sm * ctas_per_sm;
+        fin.stats = ws.stats; fin.rgba = ws.rgba; fin.depth = ws.depth; fin.init_hwc = nullptr;
+        fin.npix = W * H;
+        fin.fv = make_flag_view(ws.flags, W, H);
+        fin.depth_bg = d_depth_user;    // the caller's depth buffer: background tiles are zeroed by the finalize items
+        fin.vec = (fin.mode == 0 && fin.npix % 4 == 0 && aligned16(ws.rgba) && aligned16(ws.depth) && aligned16(fin.gt_hwc) &&
+                   aligned16(fin.x_nchw) && aligned16(fin.rgb_hwc_out)) ? 1 : 0;
         raster_kernel<<<grid, kRasterThreads, smem, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,
                                                               ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs,
-                                                              ws.ctl, ws.worklist, ws.rgba, ws.depth);
+                                                              ws.ctl, ws.worklist, ws.img_base, ws.rgba, ws.depth, B, fin);
         RAC_LAUNCHED();
     }
-    *ws_out = ws;
     return RAC_OK;
-}
-
-static FlagView make_flag_view(const unsigned* flags, int W, int H) {
-    const TileGrid tg = make_tile_grid(W, H, 1);
-    FlagView fv;
-    fv.flags = flags; fv.W = W; fv.ntx = tg.ntx; fv.nt = tg.nt;
-    return fv;
 }
 
 }  // namespace rac
@@ -232,53 +242,24 @@ size_t rac_assemble_workspace_bytes(int B) {
 int rac_render_batch(const int32_t* h_mesh_ids, const float* d_T_CO, const float* d_K, int B, int W, int H,
                      const rac_scene_t* scene, float* d_rgb_hwc, float* d_depth, uint8_t* d_rgba8,
                      void* d_ws, size_t ws_bytes, rac_stream_t stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
-    RenderWs ws;
-    int rc = render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, nullptr, d_depth, d_ws, ws_bytes, stream, &ws);
-    if (rc != RAC_OK) return rc;
-    if (d_rgb_hwc || d_rgba8 || d_depth) {   // d_depth alone still needs its background tiles zeroed
-        const int npix = W * H;
-        dim3 grid((npix + 255) / 256, B);
-        finalize_render_kernel<<<grid, 256, 0, stream>>>(ws.stats, ws.rgba, npix, d_rgb_hwc, (unsigned*)d_rgba8,
-                                                         make_flag_view(ws.flags, W, H), d_depth);
-        RAC_LAUNCHED();
-    }
-    return RAC_OK;
-}
-
-static int launch_concat(bool src_f32, const ImgStats* stats, const unsigned* rgba, const float* init_hwc,
-                         const float* depth, const float* gt, int B, int npix, int use_norm_depth,
-                         float* x, float* rgb_out, FlagView fv, float* depth_bg, cudaStream_t stream) {
-    auto aligned = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
-    const bool vec = (npix % 4 == 0) && aligned(rgba) && aligned(init_hwc) && aligned(depth) && aligned(gt) &&
-                     aligned(x) && aligned(rgb_out);
-    if (vec) {
-        dim3 grid((npix / 4 + 255) / 256, B);
-        if (src_f32)
-            finalize_concat_kernel<true><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out, fv, depth_bg);
-        else
-            finalize_concat_kernel<false><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out, fv, depth_bg);
-    } else {
-        dim3 grid((npix + 255) / 256, B);
-        if (src_f32)
-            finalize_concat_scalar_kernel<true><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out, fv, depth_bg);
-        else
-            finalize_concat_scalar_kernel<false><<<grid, 256, 0, stream>>>(stats, rgba, init_hwc, depth, gt, npix, use_norm_depth, x, rgb_out, fv, depth_bg);
-    }
-    RAC_LAUNCHED();
-    return RAC_OK;
+    FinArgs fin = {};
+    fin.mode = 1;
+    fin.rgb_hwc_out = d_rgb_hwc;
+    fin.rgba_copy = (unsigned*)d_rgba8;
+    return render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, fin, d_depth, d_ws, ws_bytes, (cudaStream_t)stream_);
 }
 
 int rac_render_concat(const int32_t* h_mesh_ids, const float* d_T_CO, const float* d_K, int B, int W, int H,
                       const rac_scene_t* scene, const float* d_gt_hwc, int use_norm_depth, float* d_x_nchw,
                       float* d_depth_out, float* d_rgb_hwc_out, void* d_ws, size_t ws_bytes, rac_stream_t stream_) {
-    cudaStream_t stream = (cudaStream_t)stream_;
     RAC_REQUIRE(d_gt_hwc && d_x_nchw, "rac_render_concat: null gt / x");
-    RenderWs ws;
-    int rc = render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, d_gt_hwc, d_depth_out, d_ws, ws_bytes, stream, &ws);
-    if (rc != RAC_OK) return rc;
-    return launch_concat(false, ws.stats, ws.rgba, nullptr, ws.depth, d_gt_hwc, B, W * H, use_norm_depth,
-                         d_x_nchw, d_rgb_hwc_out, make_flag_view(ws.flags, W, H), d_depth_out, stream);
+    FinArgs fin = {};
+    fin.mode = 0;
+    fin.gt_hwc = d_gt_hwc;
+    fin.use_norm_depth = use_norm_depth;
+    fin.x_nchw = d_x_nchw;
+    fin.rgb_hwc_out = d_rgb_hwc_out;
+    return render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, fin, d_depth_out, d_ws, ws_bytes, (cudaStream_t)stream_);
 }
 
 int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const float* d_depth, int B, int W, int H,
@@ -297,8 +278,15 @@ int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const flo
     const int chunks = (npix + 8191) / 8192;
     assemble_stats_kernel<<<dim3(chunks, B), 256, 0, stream>>>(stats, d_gt_hwc, use_norm_depth ? d_depth : nullptr, npix, chunks);
     RAC_LAUNCHED();
-    return launch_concat(true, stats, nullptr, d_init_hwc, d_depth, d_gt_hwc, B, npix, use_norm_depth, d_x_nchw, nullptr,
-                         make_flag_view(nullptr, W, H), nullptr, stream);
+    FinArgs fin = {};
+    fin.mode = 0;
+    fin.stats = stats; fin.init_hwc = d_init_hwc; fin.depth = d_depth; fin.gt_hwc = d_gt_hwc;
+    fin.npix = npix; fin.use_norm_depth = use_norm_depth; fin.x_nchw = d_x_nchw;
+    fin.fv = make_flag_view(nullptr, W, H);
+    fin.vec = (npix % 4 == 0 && aligned16(d_init_hwc) && aligned16(d_depth) && aligned16(d_gt_hwc) && aligned16(d_x_nchw)) ? 1 : 0;
+    finalize_kernel<true><<<dim3((npix + kFinChunkPix - 1) / kFinChunkPix, B), 256, 0, stream>>>(fin);
+    RAC_LAUNCHED();
+    return RAC_OK;
 }
 
 }  // extern "C"

@@ -39,7 +39,10 @@ struct ImgStats {
     unsigned dmax_bits;  // float bits of max depth (depth >= 0 so uint order == float order)
     double dsum, dsumsq; // over depth > 0.01
     double gsum, gsumsq; // over every gt value (normalize_img)
-    double pad[2];
+    unsigned ntiles;     // non-empty tiles of this image = length of its work list (appended by setup_kernel)
+    unsigned pad0;
+    unsigned tiles_done; // tiles rasterised so far; == ntiles releases the image's finalize items
+    unsigned pad;
 };
 static_assert(sizeof(ImgStats) == 64, "ImgStats must be 64 B");
 
@@ -58,11 +61,15 @@ struct TileGrid {
 
 // Device-side work-list control: setup appends non-empty tiles, the persistent raster CTAs pop them.
 struct WorkCtl {
-    unsigned n_work;     // tiles appended by setup_kernel
-    unsigned next;       // next work-list entry to rasterise
-    unsigned pad[62];
+    unsigned n_work;     // tiles appended by setup_kernel over all images (diagnostics)
+    unsigned next;       // next raster item (image-major through img_base)
+    unsigned pad[62];    // (diagnostic builds accumulate phase cycle counts here)
+    // second 256 B: finalize scheduling of the fused kernel
+    unsigned fin_next;   // next finalize item (image-major: item = b * chunks + chunk)
+    unsigned setup_done; // setup CTAs finished (the last one builds img_base)
+    unsigned pad2[62];
 };
-static_assert(sizeof(WorkCtl) == 256, "WorkCtl must be 256 B");
+static_assert(sizeof(WorkCtl) == 512, "WorkCtl must be 512 B");
 
 struct RenderWs {
     ImgStats* stats;
@@ -73,7 +80,8 @@ struct RenderWs {
     unsigned char* refs;   // [B][ncta_max][1024] local triangle ids grouped by tile
     WorkCtl* ctl;          // work-list counters (zeroed with stats and flags by one memset)
     unsigned* flags;       // [B][nt] 1 = tile has at least one triangle (raster writes it; finalize treats 0 as background)
-    unsigned* worklist;    // [B*nt] compact list of non-empty tiles, b * nt + tile, appended by setup
+    unsigned* worklist;    // [B][nt] per-image list of non-empty tiles (tile index), appended by setup
+    unsigned* img_base;    // [B+1] exclusive prefix of the per-image tile counts (last setup CTA)
     unsigned* rgba;      // [B][H][W] resolved RGBA8
     float* depth;        // [B][H][W] metric depth (may alias the caller's depth output)
     size_t zero_bytes;     // bytes from `stats` that every call zeroes (stats + ctl + flags)

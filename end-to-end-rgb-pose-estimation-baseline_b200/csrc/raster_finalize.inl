@@ -63,19 +63,46 @@ __device__ __forceinline__ bool pixel_live(const FlagView& fv, int b, int p) {
     return fv.flags[(size_t)b * fv.nt + (y / kTileH) * fv.ntx + (x / kTileW)] != 0u;
 }
 
+// Everything a finalize pass needs.  mode 0: NCHW concat (prepare_model_input), mode 1: render_batch outputs.
+struct FinArgs {
+    const ImgStats* stats;
+    const unsigned* rgba;      // resolved RGBA8 framebuffer (workspace)
+    const float* init_hwc;     // SRC_F32 only: an existing f32 HWC render
+    const float* depth;        // metric depth (workspace or the caller's buffer)
+    const float* gt_hwc;
+    int npix, use_norm_depth;
+    float* x_nchw;
+    float* rgb_hwc_out;        // mode 0: optional HWC copy of the normalised render; mode 1: the colour output
+    unsigned* rgba_copy;       // mode 1: optional RGBA8 copy
+    float* depth_bg;           // caller's depth buffer whose background tiles still need zeroing (or nullptr)
+    FlagView fv;
+    int mode, vec;
+};
+
+// ImgStats through L2 (ld.global.cg): inside the fused kernel they were produced by other SMs' atomics, and this
+// SM's L1 may hold a stale line from an earlier plain read.
+__device__ __forceinline__ ImgStats load_stats_cg(const ImgStats* p) {
+    ImgStats st;
+    const int4* src = reinterpret_cast<const int4*>(p);
+    int4* dst = reinterpret_cast<int4*>(&st);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) dst[i] = __ldcg(src + i);
+    return st;
+}
+
 // One thread = 4 consecutive pixels of one image (requires W*H % 4 == 0 and 16-B aligned planes).
 // SRC_F32: the render comes as f32 HWC (prepare_model_input on an existing render) instead of RGBA8.
 template <bool SRC_F32>
-__global__ void __launch_bounds__(256)
-finalize_concat_kernel(const ImgStats* __restrict__ stats, const unsigned* __restrict__ rgba,
-                       const float* __restrict__ init_hwc, const float* __restrict__ depth,
-                       const float* __restrict__ gt_hwc, int npix, int use_norm_depth,
-                       float* __restrict__ x_nchw, float* __restrict__ rgb_hwc_out,
-                       FlagView fv, float* __restrict__ depth_bg) {
-    const int b = blockIdx.y;
-    const int q = blockIdx.x * blockDim.x + threadIdx.x;   // quad index
-    if (4 * q >= npix) return;
-    const NormConsts n = load_norm(stats[b], (size_t)npix, use_norm_depth != 0, true);
+__device__ __forceinline__ void fin_concat_quad(const FinArgs& A, const NormConsts& n, int b, int q) {
+    const unsigned* __restrict__ rgba = A.rgba;
+    const float* __restrict__ init_hwc = A.init_hwc;
+    const float* __restrict__ depth = A.depth;
+    const float* __restrict__ gt_hwc = A.gt_hwc;
+    float* __restrict__ x_nchw = A.x_nchw;
+    float* __restrict__ rgb_hwc_out = A.rgb_hwc_out;
+    float* __restrict__ depth_bg = A.depth_bg;
+    const FlagView& fv = A.fv;
+    const int npix = A.npix, use_norm_depth = A.use_norm_depth;
     const size_t pbase = (size_t)b * npix + 4 * (size_t)q;
     const int C = use_norm_depth ? 7 : 6;
     float* xb = x_nchw + (size_t)b * C * npix + 4 * (size_t)q;
@@ -94,7 +121,7 @@ finalize_concat_kernel(const ImgStats* __restrict__ stats, const unsigned* __res
     if (use_norm_depth) {
         float4 d = make_float4(0.f, 0.f, 0.f, 0.f);
         if (any_live) {
-            d = *reinterpret_cast<const float4*>(depth + pbase);
+            d = __ldcg(reinterpret_cast<const float4*>(depth + pbase));
             if (!live[0]) d.x = 0.f; if (!live[1]) d.y = 0.f; if (!live[2]) d.z = 0.f; if (!live[3]) d.w = 0.f;
         }
         float4 o;
@@ -110,7 +137,7 @@ finalize_concat_kernel(const ImgStats* __restrict__ stats, const unsigned* __res
         r[2] = c.z; g[2] = c.w; bl[2] = e.x; r[3] = e.y; g[3] = e.z; bl[3] = e.w;
     } else {
         uint4 c = make_uint4(0u, 0u, 0u, 0u);
-        if (any_live) c = *reinterpret_cast<const uint4*>(rgba + pbase);
+        if (any_live) c = __ldcg(reinterpret_cast<const uint4*>(rgba + pbase));
         const unsigned cc[4] = {live[0] ? c.x : 0u, live[1] ? c.y : 0u, live[2] ? c.z : 0u, live[3] ? c.w : 0u};
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
@@ -142,27 +169,27 @@ finalize_concat_kernel(const ImgStats* __restrict__ stats, const unsigned* __res
 
 // scalar fallback for shapes the vector kernel cannot take (W*H % 4 != 0 or unaligned pointers)
 template <bool SRC_F32>
-__global__ void __launch_bounds__(256)
-finalize_concat_scalar_kernel(const ImgStats* __restrict__ stats, const unsigned* __restrict__ rgba,
-                              const float* __restrict__ init_hwc, const float* __restrict__ depth,
-                              const float* __restrict__ gt_hwc, int npix, int use_norm_depth,
-                              float* __restrict__ x_nchw, float* __restrict__ rgb_hwc_out,
-                              FlagView fv, float* __restrict__ depth_bg) {
-    const int b = blockIdx.y;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= npix) return;
-    const NormConsts n = load_norm(stats[b], (size_t)npix, use_norm_depth != 0, true);
+__device__ __forceinline__ void fin_concat_px(const FinArgs& A, const NormConsts& n, int b, int p) {
+    const unsigned* __restrict__ rgba = A.rgba;
+    const float* __restrict__ init_hwc = A.init_hwc;
+    const float* __restrict__ depth = A.depth;
+    const float* __restrict__ gt_hwc = A.gt_hwc;
+    float* __restrict__ x_nchw = A.x_nchw;
+    float* __restrict__ rgb_hwc_out = A.rgb_hwc_out;
+    float* __restrict__ depth_bg = A.depth_bg;
+    const FlagView& fv = A.fv;
+    const int npix = A.npix, use_norm_depth = A.use_norm_depth;
     const size_t pi = (size_t)b * npix + p;
     const int C = use_norm_depth ? 7 : 6;
     float* xb = x_nchw + (size_t)b * C * npix + p;
     int ch = 0;
     const bool live = pixel_live(fv, b, p);
     if (depth_bg && !live) depth_bg[pi] = 0.0f;
-    if (use_norm_depth) { xb[0] = norm_depth1(live ? depth[pi] : 0.0f, n); ch = 1; }
+    if (use_norm_depth) { xb[0] = norm_depth1(live ? __ldcg(depth + pi) : 0.0f, n); ch = 1; }
     float r, g, bl;
     if (SRC_F32) { r = init_hwc[3 * pi]; g = init_hwc[3 * pi + 1]; bl = init_hwc[3 * pi + 2]; }
     else {
-        const unsigned c = live ? rgba[pi] : 0u;
+        const unsigned c = live ? __ldcg(rgba + pi) : 0u;
         r = norm_col1(c & 0xFFu, n); g = norm_col1((c >> 8) & 0xFFu, n); bl = norm_col1((c >> 16) & 0xFFu, n);
     }
     xb[(size_t)(ch + 0) * npix] = r; xb[(size_t)(ch + 1) * npix] = g; xb[(size_t)(ch + 2) * npix] = bl;
@@ -173,26 +200,48 @@ finalize_concat_scalar_kernel(const ImgStats* __restrict__ stats, const unsigned
 }
 
 // render_batch API mode: f32 HWC colour (+ optional copy of the RGBA8 framebuffer)
-__global__ void __launch_bounds__(256)
-finalize_render_kernel(const ImgStats* __restrict__ stats, const unsigned* __restrict__ rgba, int npix,
-                       float* __restrict__ rgb_hwc, unsigned* __restrict__ rgba_copy,
-                       FlagView fv, float* __restrict__ depth_bg) {
-    const int b = blockIdx.y;
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= npix) return;
-    const ImgStats& st = stats[b];
-    NormConsts n;
-    n.qmax = (float)st.qmax; n.inv_qmax_valid = st.qmax > 0 ? 1.0f : 0.0f;
-    const size_t pi = (size_t)b * npix + p;
-    const bool live = pixel_live(fv, b, p);
+__device__ __forceinline__ void fin_render_px(const FinArgs& A, const NormConsts& n, int b, int p) {
+    float* __restrict__ rgb_hwc = A.rgb_hwc_out;
+    unsigned* __restrict__ rgba_copy = A.rgba_copy;
+    float* __restrict__ depth_bg = A.depth_bg;
+    const size_t pi = (size_t)b * A.npix + p;
+    const bool live = pixel_live(A.fv, b, p);
     if (depth_bg && !live) depth_bg[pi] = 0.0f;
-    const unsigned c = live ? rgba[pi] : 0u;
+    const unsigned c = live ? __ldcg(A.rgba + pi) : 0u;
     if (rgba_copy) rgba_copy[pi] = c;
     if (rgb_hwc) {
         rgb_hwc[3 * pi] = norm_col1(c & 0xFFu, n);
         rgb_hwc[3 * pi + 1] = norm_col1((c >> 8) & 0xFFu, n);
         rgb_hwc[3 * pi + 2] = norm_col1((c >> 16) & 0xFFu, n);
     }
+}
+
+// One finalize work item = kFinChunkPix consecutive pixels of image b, done by one CTA (fused into raster_kernel once
+// the image's last tile has been rasterised; also what the standalone kernel below runs per CTA).
+constexpr int kFinChunkPix = 4096;
+
+template <bool SRC_F32>
+__device__ __forceinline__ void finalize_item(const FinArgs& A, int b, int chunk) {
+    const ImgStats st = load_stats_cg(A.stats + b);
+    const NormConsts n = load_norm(st, (size_t)A.npix, A.use_norm_depth != 0, A.mode == 0);
+    const int p0 = chunk * kFinChunkPix, p1 = min(A.npix, p0 + kFinChunkPix);
+    if (A.mode == 0) {
+        if (A.vec) {
+            for (int q = (p0 >> 2) + (int)threadIdx.x; 4 * q < p1; q += (int)blockDim.x) fin_concat_quad<SRC_F32>(A, n, b, q);
+        } else {
+            for (int p = p0 + (int)threadIdx.x; p < p1; p += (int)blockDim.x) fin_concat_px<SRC_F32>(A, n, b, p);
+        }
+    } else {
+        for (int p = p0 + (int)threadIdx.x; p < p1; p += (int)blockDim.x) fin_render_px(A, n, b, p);
+    }
+}
+
+// standalone finalize: grid (chunks, B).  Used by rac_assemble_input (SRC_F32) — the render paths run the same
+// items inside raster_kernel.
+template <bool SRC_F32>
+__global__ void __launch_bounds__(256)
+finalize_kernel(FinArgs A) {
+    finalize_item<SRC_F32>(A, blockIdx.y, blockIdx.x);
 }
 
 // prepare_model_input alone: per-image gt (and depth) statistics

@@ -12,10 +12,12 @@
             g_phase_t = _t;                                                                                     \
         }                                                                                                       \
     } while (0)
+#define RAC_COUNT(idx, v) atomicAdd(reinterpret_cast<unsigned long long*>(g_phase_ctl->pad) + (idx), (unsigned long long)(v))
 #define RAC_PHASE_ARGS , WorkCtl* g_phase_ctl, long long& g_phase_t
 #define RAC_PHASE_PASS , g_phase_ctl, g_phase_t
 #else
 #define RAC_PHASE(idx) do { } while (0)
+#define RAC_COUNT(idx, v) do { } while (0)
 #define RAC_PHASE_ARGS
 #define RAC_PHASE_PASS
 #endif
@@ -487,35 +489,102 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
     }
 }
 
-// Persistent CTAs pop non-empty tiles from the work list setup_kernel built (empty tiles are never visited:
-// the finalize kernels treat a zero flag as background).
+// The fused rasterize + normalise + concat kernel.  Persistent CTAs (SMs x 4) run two kinds of work items:
+//   raster item    one non-empty tile from the work list setup_kernel built (empty tiles are never visited);
+//   finalize item  kFinChunkPix pixels of an image whose tiles have ALL been rasterised: max-normalise, normalise
+//                  depth / gt, NCHW concat with streaming stores (raster_finalize.inl).
+// Scheduling is greedy with finalize first: a CTA takes the next finalize item if its image is complete
+// (stats[b].tiles_done == ntiles), otherwise the next raster item; when the raster items are exhausted it waits for
+// the remaining images.  Raster items never wait on anything, and every item a CTA can wait for is already being
+// processed by a resident CTA, so the kernel cannot deadlock.  The effect: HBM streaming of finished images overlaps
+// the issue-bound rasterisation of later ones inside one launch.
 __global__ void __launch_bounds__(kRasterThreads, 4)
 raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
               const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
               SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
               const int4* __restrict__ recs, const unsigned* __restrict__ desc, const unsigned char* __restrict__ refs,
-              WorkCtl* __restrict__ ctl, const unsigned* __restrict__ worklist,
-              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out) {
+              WorkCtl* __restrict__ ctl, const unsigned* __restrict__ worklist, const unsigned* __restrict__ img_base,
+              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, int B, FinArgs fin) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_ctl[2];
     __shared__ unsigned s_item;
+    __shared__ int s_kind;
     __shared__ unsigned s_scan[3 * kRasterThreads + kRasterThreads / 32];
-    const unsigned n_work = ctl->n_work;    // final: written by setup_kernel (previous launch)
+    const unsigned n_work = img_base[B];    // final: written by setup_kernel (previous launch)
+    const unsigned fin_chunks = (unsigned)((fin.npix + kFinChunkPix - 1) / kFinChunkPix);
+    const unsigned fin_total = fin_chunks * (unsigned)B;
 #ifdef RAC_PHASE_TIMING
     WorkCtl* g_phase_ctl = ctl;
     long long g_phase_t = clock64();
 #endif
+    bool raster_left = true;     // thread 0 only
+    unsigned pending = 0xFFFFFFFFu;   // thread 0 only: a claimed finalize item whose image is not complete yet
+    auto image_ready = [&](unsigned f) {
+        const ImgStats* st = stats + f / fin_chunks;
+        return *(volatile const unsigned*)&st->tiles_done == st->ntiles;
+    };
     for (;;) {
-        if (threadIdx.x == 0) s_item = atomicAdd(&ctl->next, 1u);
+        if (threadIdx.x == 0) {
+            int kind = 2;
+            unsigned idx = 0;
+            for (;;) {
+                // 1. finalize first.  Items are claimed with one atomicAdd (no retry storms); a claim that lands on
+                //    an image still being rasterised is kept as `pending` while this CTA goes on rasterising, so
+                //    nothing ever blocks while raster items remain.
+                if (pending == 0xFFFFFFFFu) {
+                    const unsigned f = *(volatile unsigned*)&ctl->fin_next;
+                    if (f < fin_total && (!raster_left || image_ready(f))) {
+                        const unsigned g = atomicAdd(&ctl->fin_next, 1u);
+                        if (g < fin_total) pending = g;
+                    } else if (!raster_left && f >= fin_total) {
+                        break;                                  // nothing left of either kind
+                    }
+                }
+                if (pending != 0xFFFFFFFFu && image_ready(pending)) {
+                    kind = 1; idx = pending; pending = 0xFFFFFFFFu;
+                    RAC_COUNT(14, 1);
+                    break;
+                }
+                // 2. the next tile, image-major (so images also complete in order and their finalize items
+                //    overlap the rasterisation of later images)
+                if (raster_left) {
+                    const unsigned r = atomicAdd(&ctl->next, 1u);
+                    if (r < n_work) {
+                        int lo = 0, hi = B;          // img_base[lo] <= r < img_base[hi]
+                        while (hi - lo > 1) {
+                            const int mid = (lo + hi) >> 1;
+                            if (img_base[mid] <= r) lo = mid; else hi = mid;
+                        }
+                        kind = 0; idx = (unsigned)lo * (unsigned)tg.nt + (r - img_base[lo]);
+                        break;
+                    }
+                    raster_left = false;
+                    continue;
+                }
+                // 3. every tile has been handed out to CTAs that never block: wait for the pending image
+                if (pending != 0xFFFFFFFFu) { RAC_COUNT(16, 1); __nanosleep(100); }
+            }
+            __threadfence();                  // acquire: the image's RGBA8 / depth / stats are visible below
+            s_kind = kind; s_item = idx;
+        }
         __syncthreads();
+        const int kind = s_kind;
         const unsigned item = s_item;
-        if (item >= n_work) break;
-        const unsigned id = worklist[item];
+        if (kind == 2) break;
         RAC_PHASE(0);
-        raster_tile(smem_raw, s_ctl, s_scan, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_tri,
-                    recs, desc, refs, rgba_out, depth_out, (int)(id / (unsigned)tg.nt), (int)(id % (unsigned)tg.nt) RAC_PHASE_PASS);
-        RAC_PHASE(11);
-        __syncthreads();
-        RAC_PHASE(12);
+        if (kind == 0) {
+            const int b = (int)(item / (unsigned)tg.nt);
+            raster_tile(smem_raw, s_ctl, s_scan, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_tri,
+                        recs, desc, refs, rgba_out, depth_out, b, (int)worklist[item] RAC_PHASE_PASS);
+            RAC_PHASE(11);
+            __threadfence();                  // release this tile's stores before the completion count
+            __syncthreads();
+            if (threadIdx.x == 0) atomicAdd(&stats[b].tiles_done, 1u);
+            RAC_PHASE(12);
+        } else {
+            finalize_item<false>(fin, (int)(item / fin_chunks), (int)(item % fin_chunks));
+            __syncthreads();
+            RAC_PHASE(13);
+        }
     }
 }

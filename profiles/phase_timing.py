@@ -9,8 +9,8 @@ PKG = os.path.join(ROOT, "end-to-end-rgb-pose-estimation-baseline_b200")
 OUT = os.path.join(PKG, "librac_b200_timing.so")
 sys.path[:0] = [PKG, ROOT]
 
-NAMES = ["pop item", "descriptors+scan+gather", "coverage (flat)", "  barrier after flat", "medium tris", "large list",
-         "R1 sample analysis", "  barrier", "R2 shading", "  barrier", "R3 resolve+store", "reduce+atomics", "  barrier (loop end)"]
+NAMES = ["schedule (claim / wait)", "descriptors+scan+gather", "coverage (flat)", "  barrier after flat", "medium tris", "large list",
+         "R1 sample analysis", "  barrier", "R2 shading", "  barrier", "R3 resolve+store", "reduce+atomics", "  fence+barrier+done count", "finalize item"]
 
 
 def main():
@@ -43,6 +43,8 @@ def main():
         if it >= 2:
             tot += pad.astype(np.float64)
         print("n_work", ctl[0])
+    print("finalize claims by CAS %.0f, failed CAS %.0f, blocking claims %.0f, cycles waited in blocking claims %.0f (per iter)"
+          % tuple(tot[14:18] / 4))
     s = tot[:len(NAMES)].sum()
     for n, v in zip(NAMES, tot):
         print("%-28s %6.2f%%  %10.0f cycles/iter" % (n, 100 * v / s, v / 4))
