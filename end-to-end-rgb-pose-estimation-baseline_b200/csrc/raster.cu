@@ -19,10 +19,29 @@
 //   finalize_*       (raster_finalize.inl) streaming pass: RGBA8+depth (L2-resident) [+ gt crop] ->
 //                    normalised f32 outputs with 128-bit coalesced stores (NCHW concat or HWC render).
 #include "raster.cuh"
+#include <cooperative_groups.h>
 #include <mutex>
 #include <math.h>
+#include <stdlib.h>
 
 namespace rac {
+
+// Diagnostic builds (-DRAC_PHASE_TIMING): per-kernel [first CTA start, last CTA end] in globaltimer ns, read back with
+// rac_debug_timeline().  Kernel ids: 0 gt_norm, 1 setup, 2 raster, 3 finalize_live.
+#ifdef RAC_PHASE_TIMING
+__device__ unsigned long long g_tl[16];
+#define RAC_TL(k)                                                                  \
+    do {                                                                           \
+        if (threadIdx.x == 0) {                                                    \
+            unsigned long long _t;                                                 \
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(_t));                 \
+            atomicMin(&g_tl[2 * (k)], _t);                                         \
+            atomicMax(&g_tl[2 * (k) + 1], _t);                                     \
+        }                                                                          \
+    } while (0)
+#else
+#define RAC_TL(k) do { } while (0)
+#endif
 
 #include "raster_setup.inl"
 #include "raster_shade.inl"
@@ -42,13 +61,6 @@ static TileGrid make_tile_grid(int W, int H, int maxT) {
     tg.binned = tg.nt <= kMaxBinTiles ? 1 : 0;
     tg.ncta_max = (maxT + kSetupThreads - 1) / kSetupThreads;
     return tg;
-}
-
-static FlagView make_flag_view(const unsigned* flags, int W, int H) {
-    const TileGrid tg = make_tile_grid(W, H, 1);
-    FlagView fv;
-    fv.flags = flags; fv.W = W; fv.ntx = tg.ntx; fv.nt = tg.nt;
-    return fv;
 }
 
 static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
@@ -140,10 +152,34 @@ static int upload_ids(const int32_t* h_ids, int B, int* d_dst, cudaStream_t stre
 
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// Fork / join plumbing for the gt-normalise kernel: one library-owned non-blocking stream and two events per device.
+// Works the same in eager mode and under stream capture (the side stream joins the capture through the fork event
+// and is joined back before render_common returns).
+struct SideStream {
+    cudaStream_t stream = nullptr;
+    cudaEvent_t fork = nullptr, join = nullptr;
+};
+static SideStream g_side[64];
+
+static int side_stream(SideStream** out) {
+    int dev = 0;
+    RAC_CUDA_CHECK(cudaGetDevice(&dev));
+    RAC_REQUIRE(dev >= 0 && dev < 64, "render: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    SideStream& s = g_side[dev];
+    if (!s.stream) {
+        RAC_CUDA_CHECK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        RAC_CUDA_CHECK(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
+        RAC_CUDA_CHECK(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
+    }
+    *out = &s;
+    return RAC_OK;
+}
+
 // `fin` arrives with the caller-facing fields set (mode, outputs, gt, use_norm_depth); the workspace-side fields are
 // filled here and the whole finalize pass runs as work items of raster_kernel.
 static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const float* d_K, int B, int W, int H,
-                         const rac_scene_t* scene, FinArgs fin, float* d_depth_user,
+                         const rac_scene_t* scene, FinArgs fin,
                          void* d_ws, size_t ws_bytes, cudaStream_t stream) {
     const float* d_gt_hwc = fin.gt_hwc;
     RAC_REQUIRE(h_mesh_ids && d_T_CO && d_K, "render: null mesh ids / T_CO / K");
@@ -168,10 +204,57 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
     }
     RAC_REQUIRE((reinterpret_cast<uintptr_t>(d_ws) & 255u) == 0, "render: workspace must be 256-B aligned");
     RenderWs ws = carve_ws(d_ws, B, W, H, maxT);
-    if (d_depth_user) ws.depth = d_depth_user;   // write the metric depth straight into the caller's buffer
     const SceneConsts S = make_scene_consts(scene);
     const MeshDev* table = mesh_table_dev();
-
+    const size_t npix = (size_t)W * H;
+#ifdef RAC_PHASE_TIMING   // diagnostic builds only: RAC_DEBUG_SKIP bit mask (1 side work, 2 setup, 4 raster, 8 finalize, 16 no fork, 64 gt cluster per image)
+    const char* skip_env = getenv("RAC_DEBUG_SKIP");
+    const int skip = skip_env ? atoi(skip_env) : 0;
+#else
+    constexpr int skip = 0;
+#endif
+    // Side work — everything that does not depend on the render: the gt half of the concat (+ zero background of the
+    // render planes of x) and the zero background of the other outputs.  It runs on a forked stream under
+    // setup_kernel / raster_kernel and is joined before finalize_live_kernel overwrites the non-empty tiles.
+    static int n_sm = 0;
+    if (!n_sm) {
+        int dev = 0;
+        RAC_CUDA_CHECK(cudaGetDevice(&dev));
+        RAC_CUDA_CHECK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+    }
+    SideStream* side = nullptr;
+    {
+        int rc = side_stream(&side);
+        if (rc != RAC_OK) return rc;
+    }
+    cudaStream_t sstream = (skip & 16) ? stream : side->stream;
+    auto side_work = [&]() -> int {
+        if (skip & 1) return RAC_OK;
+        if (d_gt_hwc) {
+            // one CTA per SM (n_sm / 8 clusters), launched before setup so that it is resident next to the
+            // setup / raster CTAs for the whole call and streams in the background
+            int rc = launch_gt_norm(d_gt_hwc, fin.x_nchw, B, (int)npix, fin.use_norm_depth, 1, (skip & 64) ? 0 : n_sm / kGtCluster, sstream);
+            if (rc != RAC_OK) return rc;
+        }
+        if (fin.depth_out) RAC_CUDA_CHECK(cudaMemsetAsync(fin.depth_out, 0, sizeof(float) * npix * B, sstream));
+        if (fin.rgb_hwc_out) RAC_CUDA_CHECK(cudaMemsetAsync(fin.rgb_hwc_out, 0, sizeof(float) * 3 * npix * B, sstream));
+        if (fin.rgba_copy) RAC_CUDA_CHECK(cudaMemsetAsync(fin.rgba_copy, 0, sizeof(unsigned) * npix * B, sstream));
+        return RAC_OK;
+    };
+    static bool carve_configured = false;
+    if (!carve_configured) {
+        // every kernel of the call uses raster_kernel's L1 / shared-memory split, so that CTAs of the forked kernel and
+        // of the main chain can share an SM (an SM does not mix carve-outs)
+        RAC_CUDA_CHECK(cudaFuncSetAttribute(setup_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        RAC_CUDA_CHECK(cudaFuncSetAttribute(finalize_live_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        carve_configured = true;
+    }
+    const bool fork_early = (skip & 32) != 0;
+    if (fork_early && !(skip & 16)) {
+        RAC_CUDA_CHECK(cudaEventRecord(side->fork, stream));
+        RAC_CUDA_CHECK(cudaStreamWaitEvent(side->stream, side->fork, 0));
+        int rc = side_work(); if (rc != RAC_OK) return rc;
+    }
     RAC_CUDA_CHECK(cudaMemsetAsync(ws.stats, 0, ws.zero_bytes, stream));
     const int* d_ids = nullptr;
     if (!uniform) {
@@ -180,45 +263,45 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         d_ids = ws.mesh_ids;
     }
     const TileGrid tg = make_tile_grid(W, H, maxT);
-    if (d_gt_hwc) {   // normalize_img statistics of the gt crop (data_loaders.py:79-82), streamed once
-        const int npix = W * H;
-        const int chunks = (npix + 8191) / 8192;
-        assemble_stats_kernel<<<dim3(chunks, B), 256, 0, stream>>>(ws.stats, d_gt_hwc, nullptr, npix, chunks);
-        RAC_LAUNCHED();
-    }
-    {
+    if (!(skip & 2)) {
         dim3 grid(tg.ncta_max, B);
         setup_kernel<<<grid, kSetupThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
                                                          ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs,
                                                          ws.ctl, ws.flags, ws.worklist, ws.img_base, B);
         RAC_LAUNCHED();
     }
-    {
+    // fork AFTER setup: setup_kernel is bound by its own memory traffic (records, descriptors) and triples in
+    // duration next to a streaming kernel, while raster_kernel is issue-bound and does not notice one
+    // (profiles/kernel_timeline.py)
+    if (!fork_early && !(skip & 16)) {
+        RAC_CUDA_CHECK(cudaEventRecord(side->fork, stream));
+        RAC_CUDA_CHECK(cudaStreamWaitEvent(side->stream, side->fork, 0));
+    }
+    if (!fork_early || (skip & 16)) { int rc = side_work(); if (rc != RAC_OK) return rc; }
+    if (!(skip & 16)) RAC_CUDA_CHECK(cudaEventRecord(side->join, side->stream));
+    if (!(skip & 4)) {
         const size_t smem = kRasterSmemBytes;
-        static bool configured = false;
-        if (!configured) {
-            RAC_CUDA_CHECK(cudaFuncSetAttribute(raster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = true;
-        }
-        // persistent CTAs: as many as fit on the device, capped by the number of tiles
-        static int ctas_per_sm = 0, n_sm = 0;
+        // persistent CTAs: as many as fit on the device
+        static int ctas_per_sm = 0;
         if (!ctas_per_sm) {
-            int dev = 0;
-            RAC_CUDA_CHECK(cudaGetDevice(&dev));
-            RAC_CUDA_CHECK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
+            RAC_CUDA_CHECK(cudaFuncSetAttribute(raster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             RAC_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, raster_kernel, kRasterThreads, smem));
             if (ctas_per_sm < 1) ctas_per_sm = 1;
         }
-        const int grid = n_sm * ctas_per_sm;
-        fin.stats = ws.stats; fin.rgba = ws.rgba; fin.depth = ws.depth; fin.init_hwc = nullptr;
-        fin.npix = W * H;
-        fin.fv = make_flag_view(ws.flags, W, H);
-        fin.depth_bg = d_depth_user;    // the caller's depth buffer: background tiles are zeroed by the finalize items
-        fin.vec = (fin.mode == 0 && fin.npix % 4 == 0 && aligned16(ws.rgba) && aligned16(ws.depth) && aligned16(fin.gt_hwc) &&
-                   aligned16(fin.x_nchw) && aligned16(fin.rgb_hwc_out)) ? 1 : 0;
+        const int grid = (int)min((long long)n_sm * ctas_per_sm, (long long)B * tg.nt);
         raster_kernel<<<grid, kRasterThreads, smem, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,
                                                               ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs,
-                                                              ws.ctl, ws.worklist, ws.img_base, ws.rgba, ws.depth, B, fin);
+                                                              ws.ctl, ws.worklist, ws.img_base, ws.rgba, ws.depth, B);
+        RAC_LAUNCHED();
+    }
+    if (!(skip & 16)) RAC_CUDA_CHECK(cudaStreamWaitEvent(stream, side->join, 0));
+    if (!(skip & 8)) {
+        fin.stats = ws.stats; fin.rgba = ws.rgba; fin.depth = ws.depth; fin.init_hwc = nullptr;
+        fin.npix = (int)npix; fin.W = W;
+        fin.vec = (W % 4 == 0 && aligned16(ws.rgba) && aligned16(ws.depth) && aligned16(fin.x_nchw) &&
+                   aligned16(fin.rgb_hwc_out) && aligned16(fin.rgba_copy) && aligned16(fin.depth_out)) ? 1 : 0;
+        const int grid = (int)min((long long)n_sm * 16, (long long)B * tg.nt);
+        finalize_live_kernel<<<grid, kFinThreads, 0, stream>>>(fin, tg, H, ws.worklist, ws.img_base, B);
         RAC_LAUNCHED();
     }
     return RAC_OK;
@@ -229,6 +312,18 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
 using namespace rac;
 
 extern "C" {
+
+#ifdef RAC_PHASE_TIMING
+__attribute__((visibility("default"))) int rac_debug_timeline(unsigned long long* h_out16, int reset) {
+    if (h_out16) cudaMemcpyFromSymbol(h_out16, g_tl, sizeof(unsigned long long) * 16);
+    if (reset) {
+        unsigned long long init[16];
+        for (int i = 0; i < 16; ++i) init[i] = (i & 1 || i >= 8) ? 0ull : ~0ull;
+        cudaMemcpyToSymbol(g_tl, init, sizeof(init));
+    }
+    return 0;
+}
+#endif
 
 size_t rac_render_workspace_bytes(int B, int W, int H, int maxT) {
     if (B <= 0 || W <= 0 || H <= 0 || maxT <= 0) return 0;
@@ -246,7 +341,8 @@ int rac_render_batch(const int32_t* h_mesh_ids, const float* d_T_CO, const float
     fin.mode = 1;
     fin.rgb_hwc_out = d_rgb_hwc;
     fin.rgba_copy = (unsigned*)d_rgba8;
-    return render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, fin, d_depth, d_ws, ws_bytes, (cudaStream_t)stream_);
+    fin.depth_out = d_depth;
+    return render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, fin, d_ws, ws_bytes, (cudaStream_t)stream_);
 }
 
 int rac_render_concat(const int32_t* h_mesh_ids, const float* d_T_CO, const float* d_K, int B, int W, int H,
@@ -259,7 +355,8 @@ int rac_render_concat(const int32_t* h_mesh_ids, const float* d_T_CO, const floa
     fin.use_norm_depth = use_norm_depth;
     fin.x_nchw = d_x_nchw;
     fin.rgb_hwc_out = d_rgb_hwc_out;
-    return render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, fin, d_depth_out, d_ws, ws_bytes, (cudaStream_t)stream_);
+    fin.depth_out = d_depth_out;
+    return render_common(h_mesh_ids, d_T_CO, d_K, B, W, H, scene, fin, d_ws, ws_bytes, (cudaStream_t)stream_);
 }
 
 int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const float* d_depth, int B, int W, int H,
@@ -275,16 +372,21 @@ int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const flo
     ImgStats* stats = (ImgStats*)d_stats_ws;
     const int npix = W * H;
     RAC_CUDA_CHECK(cudaMemsetAsync(stats, 0, sizeof(ImgStats) * (size_t)B, stream));
-    const int chunks = (npix + 8191) / 8192;
-    assemble_stats_kernel<<<dim3(chunks, B), 256, 0, stream>>>(stats, d_gt_hwc, use_norm_depth ? d_depth : nullptr, npix, chunks);
-    RAC_LAUNCHED();
+    if (use_norm_depth) {
+        const int chunks = (npix + 8191) / 8192;
+        depth_stats_kernel<<<dim3(chunks, B), 256, 0, stream>>>(stats, d_depth, npix, chunks);
+        RAC_LAUNCHED();
+    }
+    {
+        int rc = launch_gt_norm(d_gt_hwc, d_x_nchw, B, npix, use_norm_depth, 0, 0, stream);
+        if (rc != RAC_OK) return rc;
+    }
     FinArgs fin = {};
     fin.mode = 0;
     fin.stats = stats; fin.init_hwc = d_init_hwc; fin.depth = d_depth; fin.gt_hwc = d_gt_hwc;
-    fin.npix = npix; fin.use_norm_depth = use_norm_depth; fin.x_nchw = d_x_nchw;
-    fin.fv = make_flag_view(nullptr, W, H);
-    fin.vec = (npix % 4 == 0 && aligned16(d_init_hwc) && aligned16(d_depth) && aligned16(d_gt_hwc) && aligned16(d_x_nchw)) ? 1 : 0;
-    finalize_kernel<true><<<dim3((npix + kFinChunkPix - 1) / kFinChunkPix, B), 256, 0, stream>>>(fin);
+    fin.npix = npix; fin.W = W; fin.use_norm_depth = use_norm_depth; fin.x_nchw = d_x_nchw;
+    fin.vec = (npix % 4 == 0 && aligned16(d_init_hwc) && aligned16(d_depth) && aligned16(d_x_nchw)) ? 1 : 0;
+    assemble_render_kernel<<<dim3((npix + kFinChunkPix - 1) / kFinChunkPix, B), 256, 0, stream>>>(fin);
     RAC_LAUNCHED();
     return RAC_OK;
 }

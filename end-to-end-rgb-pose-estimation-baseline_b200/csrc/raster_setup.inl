@@ -182,12 +182,14 @@ setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids
              int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs,
              WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ worklist,
              unsigned* __restrict__ img_base, int B) {
+    RAC_TL(1);
     setup_body(table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, znear, stats, large_tri, recs, desc, refs, ctl,
                flags, worklist);
     __shared__ unsigned s_ticket;
     __threadfence();
     __syncthreads();
     if (threadIdx.x == 0) s_ticket = atomicAdd(&ctl->setup_done, 1u);
+    RAC_TL(1);
     __syncthreads();
     if (s_ticket != gridDim.x * gridDim.y - 1u) return;
     __threadfence();

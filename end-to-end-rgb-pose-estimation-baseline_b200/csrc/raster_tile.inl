@@ -23,6 +23,7 @@
 #endif
 
 constexpr int kRasterThreads = 256;
+constexpr int kRasterRegs = 56;       // 4 CTAs/SM leave 8 K registers: one resident gt_norm CTA (256 threads x 32 regs) per SM
 constexpr int kQueueCap = 1024;       // triangle queue per flush
 constexpr int kSmallPix = 16;         // bbox∩tile pixels handled by one thread; larger -> one warp
 constexpr int kTilePix = kTileW * kTileH;
@@ -489,102 +490,54 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
     }
 }
 
-// The fused rasterize + normalise + concat kernel.  Persistent CTAs (SMs x 4) run two kinds of work items:
-//   raster item    one non-empty tile from the work list setup_kernel built (empty tiles are never visited);
-//   finalize item  kFinChunkPix pixels of an image whose tiles have ALL been rasterised: max-normalise, normalise
-//                  depth / gt, NCHW concat with streaming stores (raster_finalize.inl).
-// Scheduling is greedy with finalize first: a CTA takes the next finalize item if its image is complete
-// (stats[b].tiles_done == ntiles), otherwise the next raster item; when the raster items are exhausted it waits for
-// the remaining images.  Raster items never wait on anything, and every item a CTA can wait for is already being
-// processed by a resident CTA, so the kernel cannot deadlock.  The effect: HBM streaming of finished images overlaps
-// the issue-bound rasterisation of later ones inside one launch.
-__global__ void __launch_bounds__(kRasterThreads, 4)
+// Persistent CTAs (SMs x resident CTAs) pop non-empty tiles from the work list setup_kernel built, image-major
+// through img_base (item r belongs to image b with img_base[b] <= r < img_base[b+1]).  The claim for the NEXT item
+// is issued before the current tile is rasterised, so the atomic's round trip to L2 is hidden behind the tile.
+__global__ void __maxnreg__(kRasterRegs)
 raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
               const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
               SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
               const int4* __restrict__ recs, const unsigned* __restrict__ desc, const unsigned char* __restrict__ refs,
               WorkCtl* __restrict__ ctl, const unsigned* __restrict__ worklist, const unsigned* __restrict__ img_base,
-              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, int B, FinArgs fin) {
+              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, int B) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int s_ctl[2];
     __shared__ unsigned s_item;
-    __shared__ int s_kind;
     __shared__ unsigned s_scan[3 * kRasterThreads + kRasterThreads / 32];
     const unsigned n_work = img_base[B];    // final: written by setup_kernel (previous launch)
-    const unsigned fin_chunks = (unsigned)((fin.npix + kFinChunkPix - 1) / kFinChunkPix);
-    const unsigned fin_total = fin_chunks * (unsigned)B;
 #ifdef RAC_PHASE_TIMING
     WorkCtl* g_phase_ctl = ctl;
     long long g_phase_t = clock64();
 #endif
-    bool raster_left = true;     // thread 0 only
-    unsigned pending = 0xFFFFFFFFu;   // thread 0 only: a claimed finalize item whose image is not complete yet
-    auto image_ready = [&](unsigned f) {
-        const ImgStats* st = stats + f / fin_chunks;
-        return *(volatile const unsigned*)&st->tiles_done == st->ntiles;
-    };
-    for (;;) {
-        if (threadIdx.x == 0) {
-            int kind = 2;
-            unsigned idx = 0;
-            for (;;) {
-                // 1. finalize first.  Items are claimed with one atomicAdd (no retry storms); a claim that lands on
-                //    an image still being rasterised is kept as `pending` while this CTA goes on rasterising, so
-                //    nothing ever blocks while raster items remain.
-                if (pending == 0xFFFFFFFFu) {
-                    const unsigned f = *(volatile unsigned*)&ctl->fin_next;
-                    if (f < fin_total && (!raster_left || image_ready(f))) {
-                        const unsigned g = atomicAdd(&ctl->fin_next, 1u);
-                        if (g < fin_total) pending = g;
-                    } else if (!raster_left && f >= fin_total) {
-                        break;                                  // nothing left of either kind
-                    }
-                }
-                if (pending != 0xFFFFFFFFu && image_ready(pending)) {
-                    kind = 1; idx = pending; pending = 0xFFFFFFFFu;
-                    RAC_COUNT(14, 1);
-                    break;
-                }
-                // 2. the next tile, image-major (so images also complete in order and their finalize items
-                //    overlap the rasterisation of later images)
-                if (raster_left) {
-                    const unsigned r = atomicAdd(&ctl->next, 1u);
-                    if (r < n_work) {
-                        int lo = 0, hi = B;          // img_base[lo] <= r < img_base[hi]
-                        while (hi - lo > 1) {
-                            const int mid = (lo + hi) >> 1;
-                            if (img_base[mid] <= r) lo = mid; else hi = mid;
-                        }
-                        kind = 0; idx = (unsigned)lo * (unsigned)tg.nt + (r - img_base[lo]);
-                        break;
-                    }
-                    raster_left = false;
-                    continue;
-                }
-                // 3. every tile has been handed out to CTAs that never block: wait for the pending image
-                if (pending != 0xFFFFFFFFu) { RAC_COUNT(16, 1); __nanosleep(100); }
-            }
-            __threadfence();                  // acquire: the image's RGBA8 / depth / stats are visible below
-            s_kind = kind; s_item = idx;
-        }
-        __syncthreads();
-        const int kind = s_kind;
-        const unsigned item = s_item;
-        if (kind == 2) break;
-        RAC_PHASE(0);
-        if (kind == 0) {
-            const int b = (int)(item / (unsigned)tg.nt);
-            raster_tile(smem_raw, s_ctl, s_scan, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_tri,
-                        recs, desc, refs, rgba_out, depth_out, b, (int)worklist[item] RAC_PHASE_PASS);
-            RAC_PHASE(11);
-            __threadfence();                  // release this tile's stores before the completion count
-            __syncthreads();
-            if (threadIdx.x == 0) atomicAdd(&stats[b].tiles_done, 1u);
-            RAC_PHASE(12);
-        } else {
-            finalize_item<false>(fin, (int)(item / fin_chunks), (int)(item % fin_chunks));
-            __syncthreads();
-            RAC_PHASE(13);
-        }
+    RAC_TL(2);
+#ifdef RAC_PHASE_TIMING
+    if (threadIdx.x == 0) {      // late starters: CTAs that became resident more than 10 us after the first one
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        if (t > g_tl[4] + 10000ull) atomicAdd(&g_tl[8], 1ull);
     }
+#endif
+    if (threadIdx.x == 0) s_item = atomicAdd(&ctl->next, 1u);
+    __syncthreads();
+    for (;;) {
+        const unsigned r = s_item;
+        if (r >= n_work) break;
+        unsigned r_next = 0;
+        if (threadIdx.x == 0) r_next = atomicAdd(&ctl->next, 1u);   // consumed after the tile
+        int lo = 0, hi = B;          // img_base[lo] <= r < img_base[hi]
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (img_base[mid] <= r) lo = mid; else hi = mid;
+        }
+        const unsigned item = (unsigned)lo * (unsigned)tg.nt + (r - img_base[lo]);
+        RAC_PHASE(0);
+        raster_tile(smem_raw, s_ctl, s_scan, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_tri,
+                    recs, desc, refs, rgba_out, depth_out, lo, (int)worklist[item] RAC_PHASE_PASS);
+        RAC_PHASE(11);
+        __syncthreads();                  // every thread has read s_item (and left the tile's shared memory)
+        if (threadIdx.x == 0) s_item = r_next;
+        __syncthreads();
+        RAC_PHASE(12);
+    }
+    RAC_TL(2);
 }

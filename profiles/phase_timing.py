@@ -9,8 +9,8 @@ PKG = os.path.join(ROOT, "end-to-end-rgb-pose-estimation-baseline_b200")
 OUT = os.path.join(PKG, "librac_b200_timing.so")
 sys.path[:0] = [PKG, ROOT]
 
-NAMES = ["schedule (claim / wait)", "descriptors+scan+gather", "coverage (flat)", "  barrier after flat", "medium tris", "large list",
-         "R1 sample analysis", "  barrier", "R2 shading", "  barrier", "R3 resolve+store", "reduce+atomics", "  fence+barrier+done count", "finalize item"]
+NAMES = ["item decode", "descriptors+scan+gather", "coverage (flat)", "  barrier after flat", "medium tris", "large list",
+         "R1 sample analysis", "  barrier", "R2 shading", "  barrier", "R3 resolve+store", "reduce+atomics", "  next-item hand-over"]
 
 
 def main():
@@ -23,6 +23,8 @@ def main():
     if "--build-only" in sys.argv:
         return
     os.environ["RAC_LIB"] = OUT
+    if len(sys.argv) > 1 and sys.argv[1].isdigit():
+        os.environ["RAC_DEBUG_SKIP"] = sys.argv[1]
     import numpy as np
     import torch
     import bench
@@ -43,8 +45,6 @@ def main():
         if it >= 2:
             tot += pad.astype(np.float64)
         print("n_work", ctl[0])
-    print("finalize claims by CAS %.0f, failed CAS %.0f, blocking claims %.0f, cycles waited in blocking claims %.0f (per iter)"
-          % tuple(tot[14:18] / 4))
     s = tot[:len(NAMES)].sum()
     for n, v in zip(NAMES, tot):
         print("%-28s %6.2f%%  %10.0f cycles/iter" % (n, 100 * v / s, v / 4))
