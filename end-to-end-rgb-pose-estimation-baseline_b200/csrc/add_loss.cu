@@ -256,6 +256,7 @@ int rac_add_loss_fwd(const float* d_T_a, const float* d_T_b, const float* d_T_pr
     RAC_REQUIRE(mode >= RAC_LOSS_ADD_L1 && mode <= RAC_LOSS_DISENT_SCALED, "rac_add_loss_fwd: unknown mode %d", mode);
     RAC_REQUIRE(mode != RAC_LOSS_DISENT_SCALED || d_T_prev, "rac_add_loss_fwd: scaled mode needs T_prev");
     RAC_REQUIRE(B > 0 && N > 0, "rac_add_loss_fwd: B=%d N=%d", B, N);
+    RAC_MAX_CARVEOUT_ONCE(add_loss_fwd_kernel);
     add_loss_fwd_kernel<<<B, kLossThreads, 0, stream>>>(d_T_a, d_T_b, d_T_prev, d_pts, B, N, mode, d_per_sample, d_mean,
                                                         d_grad_a, d_grad_b, d_counter);
     RAC_LAUNCHED();
@@ -267,6 +268,7 @@ int rac_add_loss_bwd(const float* d_grad, const float* d_w, int B, float* d_gT, 
     RAC_REQUIRE(d_grad && d_w && d_gT, "rac_add_loss_bwd: null pointer");
     RAC_REQUIRE(B > 0, "rac_add_loss_bwd: B=%d", B);
     const int n16 = 16 * B;
+    RAC_MAX_CARVEOUT_ONCE(add_loss_bwd_kernel);
     add_loss_bwd_kernel<<<(n16 + 255) / 256, 256, 0, stream>>>(d_grad, d_w, n16, d_gT);
     RAC_LAUNCHED();
     return RAC_OK;

@@ -370,10 +370,13 @@ int rac_pose_update_fwd(const float* d_y, int rot_repr, const void* d_T_in, int 
     RAC_REQUIRE(rot_repr >= RAC_ROT_6D && rot_repr <= RAC_ROT_3D, "rac_pose_update_fwd: unknown rot_repr %d", rot_repr);
     RAC_REQUIRE(B > 0, "rac_pose_update_fwd: B=%d", B);
     const int threads = 64, blocks = (B + threads - 1) / threads;
-    if (t_in_is_f64)
+    if (t_in_is_f64) {
+        RAC_MAX_CARVEOUT_ONCE(pose_update_fwd_kernel<double>);
         pose_update_fwd_kernel<double><<<blocks, threads, 0, stream>>>(d_y, rot_repr, (const double*)d_T_in, fx, fy, B, d_T_out, d_saved);
-    else
+    } else {
+        RAC_MAX_CARVEOUT_ONCE(pose_update_fwd_kernel<float>);
         pose_update_fwd_kernel<float><<<blocks, threads, 0, stream>>>(d_y, rot_repr, (const float*)d_T_in, fx, fy, B, d_T_out, d_saved);
+    }
     RAC_LAUNCHED();
     return RAC_OK;
 }
@@ -384,6 +387,7 @@ int rac_pose_update_bwd(const float* d_gT_out, const float* d_saved, int rot_rep
     RAC_REQUIRE(rot_repr >= RAC_ROT_6D && rot_repr <= RAC_ROT_3D, "rac_pose_update_bwd: unknown rot_repr %d", rot_repr);
     RAC_REQUIRE(B > 0, "rac_pose_update_bwd: B=%d", B);
     const int threads = 64, blocks = (B + threads - 1) / threads;
+    RAC_MAX_CARVEOUT_ONCE(pose_update_bwd_kernel);
     pose_update_bwd_kernel<<<blocks, threads, 0, stream>>>(d_gT_out, d_saved, rot_repr, B, d_gy);
     RAC_LAUNCHED();
     return RAC_OK;

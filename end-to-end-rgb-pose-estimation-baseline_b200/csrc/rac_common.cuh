@@ -42,6 +42,19 @@ extern std::atomic<long long> g_launches;
         RAC_CUDA_CHECK(cudaGetLastError());                                         \
     } while (0)
 
+// Every kernel of the library asks for the same L1 / shared-memory split (maximum shared memory, what raster_kernel
+// needs): an SM does not mix carve-outs, so this is what lets the small pose / loss kernels of a captured step run on
+// a parallel graph branch next to the resident raster CTAs instead of waiting for an SM to drain.
+#define RAC_MAX_CARVEOUT_ONCE(kernel)                                                                       \
+    do {                                                                                                    \
+        static bool _done = false;                                                                          \
+        if (!_done) {                                                                                       \
+            RAC_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,     \
+                                                cudaSharedmemCarveoutMaxShared));                           \
+            _done = true;                                                                                   \
+        }                                                                                                   \
+    } while (0)
+
 // ---- device-resident mesh table ---------------------------------------------
 struct MeshDev {
     const float*   verts;     // V*3 object-frame positions

@@ -100,8 +100,14 @@ class RenderCompareStep:
             self._pose_loss()
         n0 = _lib.launch_count()
         with torch.cuda.graph(self._g_all):
+            # render and pose-update/loss are independent within one iteration (both read T_pred): two graph
+            # branches, so the latency-bound pose / loss kernels run under the rasteriser
+            main = torch.cuda.current_stream(self.dev)
+            s.wait_stream(main)
+            with torch.cuda.stream(s):
+                self._pose_loss()
             self._render()
-            self._pose_loss()
+            main.wait_stream(s)
         self.launches_per_run = _lib.launch_count() - n0     # librac kernels replayed by every run()
         return self
 
