@@ -21,6 +21,7 @@
 #include "raster.cuh"
 #include <cooperative_groups.h>
 #include <mutex>
+#include <type_traits>
 #include <math.h>
 #include <stdlib.h>
 
@@ -63,6 +64,22 @@ static TileGrid make_tile_grid(int W, int H, int maxT) {
     return tg;
 }
 
+static int g_raster_grid = 0;      // persistent raster CTAs (SMs x resident CTAs), fixed per process after the first query
+
+static int raster_grid() {
+    if (!g_raster_grid) {
+        int dev = 0, n_sm = 0, per_sm = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+        if (cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+        if (cudaFuncSetAttribute(raster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRasterSmemBytes) != cudaSuccess) return 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, raster_kernel, kRasterThreads, kRasterSmemBytes) != cudaSuccess) return 0;
+        if (per_sm < 1) per_sm = 1;
+        g_raster_grid = n_sm * per_sm;
+    }
+    return g_raster_grid;
+}
+constexpr int kMaxRasterGrid = 256 * 4;     // workspace is sized for this many CTAs (no device query in the size function)
+
 static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
     RenderWs w;
     char* p = (char*)base;
@@ -76,12 +93,13 @@ static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
     w.flags = (unsigned*)(p + off);          off = align256(off + sizeof(unsigned) * (size_t)B * tg.nt);
     w.zero_bytes = off;
     w.worklist = (unsigned*)(p + off);       off = align256(off + sizeof(unsigned) * (size_t)B * tg.nt);
-    w.img_base = (unsigned*)(p + off);       off = align256(off + sizeof(unsigned) * ((size_t)B + 1));
     w.mesh_ids = (int*)(p + off);            off = align256(off + sizeof(int) * (size_t)B);
+    w.large_cnt = (unsigned*)(p + off);      off = align256(off + sizeof(unsigned) * (size_t)B * tg.ncta_max);
     w.large_tri = (unsigned*)(p + off);      off = align256(off + sizeof(unsigned) * (size_t)B * maxT);
     w.recs = (int4*)(p + off);               off = align256(off + sizeof(int4) * 3 * (size_t)B * maxT);
     w.desc = (unsigned*)(p + off);           off = align256(off + sizeof(unsigned) * ndesc);
     w.refs = (unsigned char*)(p + off);      off = align256(off + nrefs);
+    w.scratch_col = (unsigned*)(p + off);    off = align256(off + sizeof(unsigned) * kScratchPerCta * (size_t)kMaxRasterGrid);
     w.rgba = (unsigned*)(p + off);           off = align256(off + sizeof(unsigned) * (size_t)B * W * H);
     w.depth = (float*)(p + off);             off = align256(off + sizeof(float) * (size_t)B * W * H);
     w.total = off;
@@ -186,6 +204,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
     RAC_REQUIRE(B > 0 && W > 0 && H > 0, "render: B=%d W=%d H=%d must be positive", B, W, H);
     RAC_REQUIRE(W <= 8192 && H <= 8192, "render: image %dx%d exceeds the 8192 px limit", W, H);
     RAC_REQUIRE(B <= 65535, "render: B=%d exceeds 65535 (grid.y)", B);
+    RAC_REQUIRE((double)B * ((W + kTileW - 1) / kTileW) * ((H + kTileH - 1) / kTileH) < 4.0e9, "render: B x bins exceeds 2^32");
     int maxT = 0;
     bool uniform = true;
     for (int i = 0; i < B; ++i) {
@@ -266,8 +285,8 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
     if (!(skip & 2)) {
         dim3 grid(tg.ncta_max, B);
         setup_kernel<<<grid, kSetupThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
-                                                         ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs,
-                                                         ws.ctl, ws.flags, ws.worklist, ws.img_base, B);
+                                                         ws.stats, ws.large_cnt, ws.large_tri, ws.recs, ws.desc, ws.refs,
+                                                         ws.ctl, ws.flags, ws.worklist);
         RAC_LAUNCHED();
     }
     // fork AFTER setup: setup_kernel is bound by its own memory traffic (records, descriptors) and triples in
@@ -280,18 +299,12 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
     if (!fork_early || (skip & 16)) { int rc = side_work(); if (rc != RAC_OK) return rc; }
     if (!(skip & 16)) RAC_CUDA_CHECK(cudaEventRecord(side->join, side->stream));
     if (!(skip & 4)) {
-        const size_t smem = kRasterSmemBytes;
-        // persistent CTAs: as many as fit on the device
-        static int ctas_per_sm = 0;
-        if (!ctas_per_sm) {
-            RAC_CUDA_CHECK(cudaFuncSetAttribute(raster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            RAC_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&ctas_per_sm, raster_kernel, kRasterThreads, smem));
-            if (ctas_per_sm < 1) ctas_per_sm = 1;
-        }
-        const int grid = (int)min((long long)n_sm * ctas_per_sm, (long long)B * tg.nt);
-        raster_kernel<<<grid, kRasterThreads, smem, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,
-                                                              ws.stats, ws.large_tri, ws.recs, ws.desc, ws.refs,
-                                                              ws.ctl, ws.worklist, ws.img_base, ws.rgba, ws.depth, B);
+        const int grid_max = raster_grid();
+        RAC_REQUIRE(grid_max > 0 && grid_max <= kMaxRasterGrid, "render: raster grid query failed (%d)", grid_max);
+        const int grid = (int)min((long long)grid_max, (long long)B * tg.nt);
+        raster_kernel<<<grid, kRasterThreads, kRasterSmemBytes, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,
+                                                                          ws.stats, ws.large_cnt, ws.large_tri, ws.recs, ws.desc, ws.refs,
+                                                                          ws.ctl, ws.worklist, ws.rgba, ws.depth, ws.scratch_col);
         RAC_LAUNCHED();
     }
     if (!(skip & 16)) RAC_CUDA_CHECK(cudaStreamWaitEvent(stream, side->join, 0));
@@ -301,7 +314,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         fin.vec = (W % 4 == 0 && aligned16(ws.rgba) && aligned16(ws.depth) && aligned16(fin.x_nchw) &&
                    aligned16(fin.rgb_hwc_out) && aligned16(fin.rgba_copy) && aligned16(fin.depth_out)) ? 1 : 0;
         const int grid = (int)min((long long)n_sm * 16, (long long)B * tg.nt);
-        finalize_live_kernel<<<grid, kFinThreads, 0, stream>>>(fin, tg, H, ws.worklist, ws.img_base, B);
+        finalize_live_kernel<<<grid, kFinThreads, 0, stream>>>(fin, tg, H, ws.worklist, ws.ctl);
         RAC_LAUNCHED();
     }
     return RAC_OK;

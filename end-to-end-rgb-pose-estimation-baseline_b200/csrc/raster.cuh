@@ -33,16 +33,12 @@ constexpr int kMaxBinTiles = 2048;    // images with more tiles (> 2 Mpx) skip b
 
 // per-image accumulators, zeroed at the start of every call
 struct ImgStats {
-    unsigned nlarge;     // survivors spanning more than 2x2 tiles (per-image large list)
+    unsigned nlarge;     // large triangles of the image (all setup CTAs); 0 lets the bins skip the large-list scan
     unsigned qmax;       // max resolved 8-bit colour value (R9)
     unsigned dcount;     // #pixels with depth > 0.01      (normalize_depth mask)
     unsigned dmax_bits;  // float bits of max depth (depth >= 0 so uint order == float order)
     double dsum, dsumsq; // over depth > 0.01
-    double gsum, gsumsq; // over every gt value (normalize_img)
-    unsigned ntiles;     // non-empty tiles of this image = length of its work list (appended by setup_kernel)
-    unsigned pad0;
-    unsigned tiles_done; // tiles rasterised so far; == ntiles releases the image's finalize items
-    unsigned pad;
+    double pad1[4];
 };
 static_assert(sizeof(ImgStats) == 64, "ImgStats must be 64 B");
 
@@ -56,34 +52,31 @@ struct TriRec {
 struct TileGrid {
     int ntx, nty, nt;
     int binned;
-    int ncta_max;        // ceil(maxT / kSetupThreads): stride of the descriptor / ref tables
+    int ncta_max;        // ceil(maxT / kSetupThreads): stride of the descriptor / ref / large-list tables
 };
 
-// Device-side work-list control: setup appends non-empty tiles, the persistent raster CTAs pop them.
+// Device-side work-list control: setup appends non-empty bins, the persistent raster warps pop their quarters.
 struct WorkCtl {
-    unsigned n_work;     // tiles appended by setup_kernel over all images (diagnostics)
-    unsigned next;       // next raster item (image-major through img_base)
+    unsigned n_work;     // bins appended by setup_kernel over all images
+    unsigned next;       // next raster item (4 per bin)
     unsigned pad[62];    // (diagnostic builds accumulate phase cycle counts here)
-    // second 256 B: finalize scheduling of the fused kernel
-    unsigned fin_next;   // next finalize item (image-major: item = b * chunks + chunk)
-    unsigned setup_done; // setup CTAs finished (the last one builds img_base)
-    unsigned pad2[62];
 };
-static_assert(sizeof(WorkCtl) == 512, "WorkCtl must be 512 B");
+static_assert(sizeof(WorkCtl) == 256, "WorkCtl must be 256 B");
 
 struct RenderWs {
     ImgStats* stats;
     int* mesh_ids;
-    unsigned* large_tri;   // [B][maxT] triangle ids of the per-image large list
+    unsigned* large_cnt;   // [B][ncta_max] large triangles found by each setup CTA
+    unsigned* large_tri;   // [B][maxT] their ids: slice [cta * 256, cta * 256 + large_cnt) per setup CTA
     int4* recs;            // [B][maxT][3]
-    unsigned* desc;        // [B][nt][ncta_max]  (offset << 16) | count, one per (tile, setup CTA)
-    unsigned char* refs;   // [B][ncta_max][1024] local triangle ids grouped by tile
+    unsigned* desc;        // [B][nt][ncta_max]  (offset << 16) | count, one per (bin, setup CTA)
+    unsigned char* refs;   // [B][ncta_max][1024] local triangle ids grouped by bin
     WorkCtl* ctl;          // work-list counters (zeroed with stats and flags by one memset)
-    unsigned* flags;       // [B][nt] 1 = tile has at least one triangle (raster writes it; finalize treats 0 as background)
-    unsigned* worklist;    // [B][nt] per-image list of non-empty tiles (tile index), appended by setup
-    unsigned* img_base;    // [B+1] exclusive prefix of the per-image tile counts (last setup CTA)
-    unsigned* rgba;      // [B][H][W] resolved RGBA8
-    float* depth;        // [B][H][W] metric depth (may alias the caller's depth output)
+    unsigned* flags;       // [B][nt] 1 = bin is on the work list
+    unsigned* worklist;    // [B * nt] non-empty bins (image * nt + bin), appended by setup
+    unsigned* scratch_col; // [raster CTAs][4][512] committed colours of bins with more than 254 triangles
+    unsigned* rgba;        // [B][H][W] resolved RGBA8 (non-empty bins only)
+    float* depth;          // [B][H][W] metric depth (non-empty bins only)
     size_t zero_bytes;     // bytes from `stats` that every call zeroes (stats + ctl + flags)
     size_t total;
 };

@@ -73,21 +73,15 @@ __device__ __forceinline__ ImgStats load_stats_cg(const ImgStats* p) {
 constexpr int kFinThreads = 128;
 
 __global__ void __launch_bounds__(kFinThreads)
-finalize_live_kernel(FinArgs A, TileGrid tg, int H, const unsigned* __restrict__ worklist,
-                     const unsigned* __restrict__ img_base, int B) {
+finalize_live_kernel(FinArgs A, TileGrid tg, int H, const unsigned* __restrict__ worklist, const WorkCtl* __restrict__ ctl) {
     RAC_TL(3);
-    const unsigned n_work = img_base[B];
+    const unsigned n_work = __ldcg(&ctl->n_work);
     const int W = A.W, npix = A.npix;
     const int C = A.use_norm_depth ? 7 : 6;
     const int ly = threadIdx.x >> 3, lx = (threadIdx.x & 7) << 2;
     for (unsigned r = blockIdx.x; r < n_work; r += gridDim.x) {
-        int lo = 0, hi = B;
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (img_base[mid] <= r) lo = mid; else hi = mid;
-        }
-        const int b = lo;
-        const int tile = (int)worklist[(size_t)b * tg.nt + (r - img_base[b])];
+        const unsigned e = worklist[r];
+        const int b = (int)(e / (unsigned)tg.nt), tile = (int)(e % (unsigned)tg.nt);
         const int x = (tile % tg.ntx) * kTileW + lx, y = (tile / tg.ntx) * kTileH + ly;
         if (y >= H || x >= W) continue;
         const ImgStats st = load_stats_cg(A.stats + b);

@@ -38,25 +38,23 @@ __device__ __forceinline__ bool project_vertex(const CamPose& c, const float* __
     return true;
 }
 
-// First triangle to touch a tile appends it to the raster work list.
-__device__ __forceinline__ void mark_tile(WorkCtl* ctl, ImgStats* st, unsigned* flags, unsigned* worklist,
-                                          unsigned img_base, unsigned tile) {
-    if (flags[img_base + tile] == 0u && atomicExch(&flags[img_base + tile], 1u) == 0u) {
-        worklist[img_base + atomicAdd(&st->ntiles, 1u)] = tile;
-        atomicAdd(&ctl->n_work, 1u);
-    }
+// First triangle to touch a tile appends (image, tile) to the flat raster work list.
+__device__ __forceinline__ void mark_tile(WorkCtl* ctl, unsigned* flags, unsigned* worklist, unsigned b, unsigned nt, unsigned tile) {
+    unsigned* f = flags + (size_t)b * nt + tile;
+    if (*f == 0u && atomicExch(f, 1u) == 0u) worklist[atomicAdd(&ctl->n_work, 1u)] = b * nt + tile;
 }
 
 // One CTA = kSetupThreads consecutive triangles of one image.  Survivors that touch at most 2x2 tiles are
 // binned: the CTA counts them per tile in shared memory, scans the counts, and publishes
 //   desc[b][tile][cta] = (offset << 16) | count      (offset into the CTA's private 1024-B ref region)
 //   refs[b][cta][offset + k] = local triangle id (u8) (triangle = cta * 256 + id)
-// with plain stores — no global atomics, nothing to zero beforehand.  The others are appended to the image's
-// large list (rare for ModelNet-scale meshes; the common case for 12-triangle boxes).
+// with plain stores — no global atomics, nothing to zero beforehand.  The others ("large": rare for ModelNet-scale
+// meshes, the common case for 12-triangle boxes) are compacted, in triangle order, into the CTA's slice of the image's
+// large list: large_tri[b][cta * 256 + k], k < large_cnt[b][cta] — deterministic, unlike an atomic append.
 __device__ __forceinline__ void
 setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
-             float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_tri,
+             float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_cnt, unsigned* __restrict__ large_tri,
              int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs,
              WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ worklist) {
     __shared__ unsigned s_cnt[kMaxBinTiles];
@@ -125,17 +123,27 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         for (int ty = ty0; ty <= ty1; ++ty)
             for (int tx = tx0; tx <= tx1; ++tx) slot[k++] = atomicAdd(&s_cnt[ty * tg.ntx + tx], 1u);
     }
-    // warp-aggregated append of large triangles to the image's large list
+    // large triangles: CTA-level compaction in triangle order
+    __shared__ unsigned s_lwarp[kSetupThreads / 32];
     const unsigned m = __ballot_sync(0xffffffffu, large);
-    if (m) {
-        const int leader = __ffs(m) - 1;
-        unsigned base = 0;
-        if (lane == leader) base = atomicAdd(&stats[b].nlarge, (unsigned)__popc(m));
-        base = __shfl_sync(0xffffffffu, base, leader);
+    if (lane == 0) s_lwarp[warp] = (unsigned)__popc(m);
+    __syncthreads();
+    {
+        unsigned base = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kSetupThreads / 32; ++w) {
+            const unsigned v = s_lwarp[w];
+            if (w < warp) base += v;
+            total += v;
+        }
+        if (tid == 0) {
+            large_cnt[(size_t)b * tg.ncta_max + blockIdx.x] = total;
+            if (total) atomicAdd(&stats[b].nlarge, total);
+        }
         if (large) {
-            large_tri[(size_t)b * maxT + base + __popc(m & ((1u << lane) - 1u))] = (unsigned)t;
+            large_tri[(size_t)b * maxT + (size_t)blockIdx.x * kSetupThreads + base + __popc(m & ((1u << lane) - 1u))] = (unsigned)t;
             for (int ty = ty0; ty <= ty1; ++ty)
-                for (int tx = tx0; tx <= tx1; ++tx) mark_tile(ctl, stats + b, flags, worklist, (unsigned)(b * tg.nt), (unsigned)(ty * tg.ntx + tx));
+                for (int tx = tx0; tx <= tx1; ++tx) mark_tile(ctl, flags, worklist, (unsigned)b, (unsigned)tg.nt, (unsigned)(ty * tg.ntx + tx));
         }
     }
     if (!tg.binned) return;   // CTA-uniform
@@ -160,7 +168,7 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         const unsigned c = s_cnt[i];
         s_off[i] = run;
         dimg[(size_t)i * tg.ncta_max] = (run << 16) | c;    // offset <= 1024, count <= 256
-        if (c) mark_tile(ctl, stats + b, flags, worklist, (unsigned)(b * tg.nt), (unsigned)i);
+        if (c) mark_tile(ctl, flags, worklist, (unsigned)b, (unsigned)tg.nt, (unsigned)i);
         run += c;
     }
     __syncthreads();
@@ -172,42 +180,14 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
     }
 }
 
-// After its share of the work every CTA takes a ticket; the last one turns the per-image tile counts into the
-// image-major prefix img_base[0..B] that lets raster_kernel hand out all tiles with one global counter
-// (item r belongs to the image b with img_base[b] <= r < img_base[b+1]).
 __global__ void __launch_bounds__(kSetupThreads)
 setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
-             float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_tri,
+             float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_cnt, unsigned* __restrict__ large_tri,
              int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs,
-             WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ worklist,
-             unsigned* __restrict__ img_base, int B) {
+             WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ worklist) {
     RAC_TL(1);
-    setup_body(table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, znear, stats, large_tri, recs, desc, refs, ctl,
+    setup_body(table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, znear, stats, large_cnt, large_tri, recs, desc, refs, ctl,
                flags, worklist);
-    __shared__ unsigned s_ticket;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) s_ticket = atomicAdd(&ctl->setup_done, 1u);
     RAC_TL(1);
-    __syncthreads();
-    if (s_ticket != gridDim.x * gridDim.y - 1u) return;
-    __threadfence();
-    if (threadIdx.x < 32) {
-        const int lane = threadIdx.x;
-        unsigned carry = 0;
-        for (int b0 = 0; b0 < B; b0 += 32) {
-            const int bi = b0 + lane;
-            const unsigned c = bi < B ? __ldcg(&stats[bi].ntiles) : 0u;
-            unsigned incl = c;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += v;
-            }
-            if (bi < B) img_base[bi] = carry + incl - c;
-            carry += __shfl_sync(0xffffffffu, incl, 31);
-        }
-        if (lane == 0) img_base[B] = carry;
-    }
 }

@@ -67,32 +67,9 @@ __device__ __forceinline__ void persp_bary(const TriGeom& g, int Px, int Py, flo
     w0 = a0 * inv; w1 = a1 * inv; w2 = a2 * inv;
 }
 
-// RS-S: shade triangle `tri` at the centre of pixel (px,py); returns RGBA8 packed little-endian.
-__device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __restrict__ rec, unsigned tri, int px, int py) {
-    const int4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
-    const TriGeom g = unpack_geom(q0, q1, q2);
-    const float nx = __int_as_float(q2.y), ny = __int_as_float(q2.z), nz = __int_as_float(q2.w);
-    const int Pcx = px * kSubpix + 128, Pcy = py * kSubpix + 128;
-    float iz = fmaf(g.gy, (float)(Pcy - g.Y0), fmaf(g.gx, (float)(Pcx - g.X0), g.iz0));
-    iz = fminf(fmaxf(iz, sc.iz_min), sc.iz_max);
-    const float z = __fdividef(1.0f, iz);   // fast-math shading: colour parity bar is 2/255 (north_star), not bit-exactness
-    const float x = ((px + 0.5f) - sc.cx) * sc.fx_inv * z;
-    const float y = ((py + 0.5f) - sc.cy) * sc.fy_inv * z;
-    const float dist2 = x * x + y * y + z * z;
-    const float inv_d = rsqrtf(dist2);
-    // camera and light sit at the origin: l = v = h = -p/|p|
-    const float ndl = -(nx * x + ny * y + nz * z) * inv_d;
-    const float nl = fminf(fmaxf(ndl, 0.001f), 1.0f);
-    const float nv = fminf(fmaxf(fabsf(ndl), 0.001f), 1.0f);
-    const float nh = clamp01(ndl);
-    // spot cone around the camera's forward axis (+z in the OpenCV frame)
-    const float cd = clamp01(z * inv_d);
-    float att = clamp01(cd * sc.las + sc.lao);
-    att = att * att * (inv_d * inv_d);
-    const float radiance = att * sc.intensity;
-
-    float base[3] = {sc.base[0], sc.base[1], sc.base[2]};
-    if (sc.vcolor || sc.tex) {
+// COLOR_0 / texture modulation of the base colour (R7 "x COLOR_0", R8) at subpixel point (Pcx, Pcy).  Kept out of line:
+// the raster warps of an SM run at unrelated program counters, so the kernel's hot instruction footprint matters.
+__device__ __noinline__ void shade_base_color(const ShadeCtx& sc, const TriGeom& g, unsigned tri, int Pcx, int Pcy, float* base) {
         float w0, w1, w2;
         persp_bary(g, Pcx, Pcy, w0, w1, w2);
         // record order is (v0, v2, v1) of the mesh face (setup swaps v1 <-> v2)
@@ -135,7 +112,34 @@ __device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __rest
             base[1] *= srgb_to_linear(ta.y);
             base[2] *= srgb_to_linear(ta.z);
         }
-    }
+}
+
+// RS-S: shade triangle `tri` at the centre of pixel (px,py); returns RGBA8 packed little-endian.
+__device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __restrict__ rec, unsigned tri, int px, int py) {
+    const int4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
+    const TriGeom g = unpack_geom(q0, q1, q2);
+    const float nx = __int_as_float(q2.y), ny = __int_as_float(q2.z), nz = __int_as_float(q2.w);
+    const int Pcx = px * kSubpix + 128, Pcy = py * kSubpix + 128;
+    float iz = fmaf(g.gy, (float)(Pcy - g.Y0), fmaf(g.gx, (float)(Pcx - g.X0), g.iz0));
+    iz = fminf(fmaxf(iz, sc.iz_min), sc.iz_max);
+    const float z = __fdividef(1.0f, iz);   // fast-math shading: colour parity bar is 2/255 (north_star), not bit-exactness
+    const float x = ((px + 0.5f) - sc.cx) * sc.fx_inv * z;
+    const float y = ((py + 0.5f) - sc.cy) * sc.fy_inv * z;
+    const float dist2 = x * x + y * y + z * z;
+    const float inv_d = rsqrtf(dist2);
+    // camera and light sit at the origin: l = v = h = -p/|p|
+    const float ndl = -(nx * x + ny * y + nz * z) * inv_d;
+    const float nl = fminf(fmaxf(ndl, 0.001f), 1.0f);
+    const float nv = fminf(fmaxf(fabsf(ndl), 0.001f), 1.0f);
+    const float nh = clamp01(ndl);
+    // spot cone around the camera's forward axis (+z in the OpenCV frame)
+    const float cd = clamp01(z * inv_d);
+    float att = clamp01(cd * sc.las + sc.lao);
+    att = att * att * (inv_d * inv_d);
+    const float radiance = att * sc.intensity;
+
+    float base[3] = {sc.base[0], sc.base[1], sc.base[2]};
+    if (sc.vcolor || sc.tex) shade_base_color(sc, g, tri, Pcx, Pcy, base);   // out of line: cold for untextured meshes
 
     // metallic-roughness BRDF with v = l = h: vh = 1 -> Fresnel = f0
     const float kk = sc.kgeo;

@@ -1,5 +1,20 @@
-// raster_tile.inl — raster_kernel: one CTA per (image, 32x16-px tile) work item.  Spec: RS-C, RS-Z, RS-R in raster.cuh.
+// raster_tile.inl — raster_kernel: one CTA per (image, 32x16-px bin) work item.  Spec: RS-C, RS-Z, RS-R in raster.cuh.
 // Included by raster.cu (inside namespace rac).
+//
+//   gather    the bin's descriptors (one per setup CTA) -> u8 ref regions -> triangle ids in a shared queue;
+//   coverage  batches of <= 254 triangles, thread = triangle: triangles with <= 16 bbox pixels are staged (int32 edge
+//             equations relative to the clipped bbox) and their (triangle, pixel) items flattened over the warp, 32
+//             per step; larger ones are walked by a whole warp each.  Exact edge functions, top-left rule, 4 samples;
+//   depth     24-bit depth and the triangle's batch-local id form one 32-bit key (d24 << 8 | id): the z-test is ONE
+//             native shared-memory atomic (ATOMS.MIN.U32), no 64-bit CAS loop.  Ids follow the triangle order, so
+//             ties go to the lower triangle index (GL's in-order rasterisation);
+//   resolve   per pixel the distinct winners among the 4 samples are listed, the (pixel, triangle) items are shaded
+//             256 per step (flattened again), colours averaged, RGBA8 + f32 depth stored as 128-B row segments, and
+//             the per-image max / depth statistics reduced -> one atomic per accumulator per bin.
+// A bin with more than 254 triangles commits between batches: the current winners are shaded, their colours parked in
+// the CTA's global scratch and their ids cleared (id 0 = committed: a later triangle at the same depth loses, as
+// in-order rasterisation would have it).  The warp-autonomous alternative (one warp per 16x8 sub-tile, no barriers)
+// was built and measured slower: see profiles/README.md.
 
 // Optional phase timeline (build with -DRAC_PHASE_TIMING): thread 0 of every CTA accumulates clock64() deltas per
 // phase into WorkCtl::pad (read back from the workspace by profiles/phase_timing.py).  Off in the product build.
@@ -12,32 +27,36 @@
             g_phase_t = _t;                                                                                     \
         }                                                                                                       \
     } while (0)
-#define RAC_COUNT(idx, v) atomicAdd(reinterpret_cast<unsigned long long*>(g_phase_ctl->pad) + (idx), (unsigned long long)(v))
 #define RAC_PHASE_ARGS , WorkCtl* g_phase_ctl, long long& g_phase_t
 #define RAC_PHASE_PASS , g_phase_ctl, g_phase_t
 #else
 #define RAC_PHASE(idx) do { } while (0)
-#define RAC_COUNT(idx, v) do { } while (0)
 #define RAC_PHASE_ARGS
 #define RAC_PHASE_PASS
 #endif
 
 constexpr int kRasterThreads = 256;
-constexpr int kRasterRegs = 56;       // 4 CTAs/SM leave 8 K registers: one resident gt_norm CTA (256 threads x 32 regs) per SM
-constexpr int kQueueCap = 1024;       // triangle queue per flush
-constexpr int kSmallPix = 16;         // bbox∩tile pixels handled by one thread; larger -> one warp
+constexpr int kRasterWarpsN = kRasterThreads / 32;
+constexpr int kQueueCap = 1024;       // triangle ids gathered per round
+constexpr int kBatch = 254;           // triangles per coverage batch = local ids 1..254 (0 = committed, 0xFF = the empty key)
+constexpr int kSmallPix = 16;         // bbox∩bin pixels handled as flattened items; larger -> one warp per triangle
 constexpr int kTilePix = kTileW * kTileH;
+constexpr int kTriStride = 20;        // words per staged triangle (16 used; 80 B keeps LDS.128 aligned and conflict-free)
+constexpr unsigned kKeyEmpty32 = 0xFFFFFFFFu;
+constexpr int kScratchPerCta = 4 * kTilePix;     // u32 colours of committed samples (global, per persistent CTA)
 
-__device__ __forceinline__ void smem_min64(unsigned long long* addr, unsigned long long v) {
-    unsigned long long old = *(volatile unsigned long long*)addr;
-    while (v < old) {
-        const unsigned long long assumed = old;
-        old = atomicCAS(addr, assumed, v);
-        if (old == assumed) break;
-    }
-}
+// dynamic shared memory of one CTA
+struct __align__(16) RasterSmem {
+    unsigned z[4 * kTilePix];                      //  8 KB keys, sample-major: z[s * 512 + p]
+    int queue[kQueueCap];                          //  4 KB gathered triangle ids
+    int medq[kRasterThreads];                      //  1 KB batch-local ids of medium triangles
+    int tri[kRasterThreads * kTriStride];          // 20 KB staged triangles of the current batch
+    unsigned short items[kRasterWarpsN * 32 * kSmallPix];   // 8 KB per-warp flattened (triangle, pixel) items; resolve: (pixel, sample) items
+    unsigned slots[kBatch + 1];                    //  1 KB local id - 1 -> triangle id
+};
+constexpr size_t kRasterSmemBytes = sizeof(RasterSmem);
 
-// bbox (in pixels) of the triangle clipped to the tile [x_lo, x_hi] x [y_lo, y_hi]
+// bbox (in pixels) of the triangle clipped to the bin [x_lo, x_hi] x [y_lo, y_hi]
 __device__ __forceinline__ void tri_bbox(const TriGeom& g, int x_lo, int x_hi, int y_lo, int y_hi,
                                          int& bx0, int& bx1, int& by0, int& by1) {
     const int xmin = min(g.X0, min(g.X1, g.X2)), xmax = max(g.X0, max(g.X1, g.X2));
@@ -48,13 +67,21 @@ __device__ __forceinline__ void tri_bbox(const TriGeom& g, int x_lo, int x_hi, i
     by1 = min(floor_div256(ymax - 32), y_hi);
 }
 
-// RS-C + RS-Z for one triangle over its bbox∩tile, `nl` lanes cooperating (lane in [0,nl)).
+// RS-Z for one covered sample -> key, or kKeyEmpty32 when the depth is outside [0, 1)
+__device__ __forceinline__ unsigned depth_key(float iz, float c0, float c1, unsigned local) {
+    const float d = __fmaf_rn(-c1, iz, c0);
+    if (d >= 0.0f && d <= 1.0f) {
+        const unsigned d24 = (unsigned)__float2int_rn(__fmul_rn(d, 16777215.0f));
+        if (d24 < kDepthMax) return (d24 << 8) | local;
+    }
+    return kKeyEmpty32;
+}
+
+// RS-C + RS-Z for one triangle over its bbox∩bin, one warp cooperating (lane = pixel).
 // I = int for binned triangles (extent <= 64 px: every product < 2^29), long long for large ones.
-// keys: [4][kTilePix] sample-major visibility buffer of this tile (origin tile_x0, tile_y0).
 template <typename I>
-__device__ __forceinline__ void raster_tri(const TriGeom& g, unsigned tri, int bx0, int bx1, int by0, int by1,
-                                           int lane, int nl, unsigned long long* keys, int tile_x0, int tile_y0,
-                                           float c0, float c1) {
+__device__ __forceinline__ void raster_tri_warp(const TriGeom& g, unsigned local, int bx0, int bx1, int by0, int by1,
+                                                int lane, unsigned* z, int x_lo, int y_lo, float c0, float c1) {
     // edges e0: v0->v1, e1: v1->v2, e2: v2->v0;  E(P) = dx (Py-ay) - dy (Px-ax), interior E >= 0
     const I dx0 = g.X1 - g.X0, dy0 = g.Y1 - g.Y0;
     const I dx1 = g.X2 - g.X1, dy1 = g.Y2 - g.Y1;
@@ -67,14 +94,14 @@ __device__ __forceinline__ void raster_tri(const TriGeom& g, unsigned tri, int b
     const int n = w * (by1 - by0 + 1);
     constexpr int SX[4] = {96, 224, 32, 160};
     constexpr int SY[4] = {32, 96, 160, 224};
-    for (int i = lane; i < n; i += nl) {
+    for (int i = lane; i < n; i += 32) {
         const int ry = i / w;
         const int px = bx0 + (i - ry * w), py = by0 + ry;
         const int ox = px * kSubpix, oy = py * kSubpix;
         const I E0 = dx0 * (I)(oy - g.Y0) - dy0 * (I)(ox - g.X0) + b0;
         const I E1 = dx1 * (I)(oy - g.Y1) - dy1 * (I)(ox - g.X1) + b1;
         const I E2 = dx2 * (I)(oy - g.Y2) - dy2 * (I)(ox - g.X2) + b2;
-        const int pidx = (py - tile_y0) * kTileW + (px - tile_x0);
+        const int pidx = (py - y_lo) * kTileW + (px - x_lo);
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
             const I e0 = E0 + dx0 * (I)SY[s] - dy0 * (I)SX[s];
@@ -83,123 +110,89 @@ __device__ __forceinline__ void raster_tri(const TriGeom& g, unsigned tri, int b
             if ((e0 | e1 | e2) >= 0) {
                 const float fxr = (float)(ox + SX[s] - g.X0), fyr = (float)(oy + SY[s] - g.Y0);
                 const float iz = __fmaf_rn(g.gy, fyr, __fmaf_rn(g.gx, fxr, g.iz0));
-                const float d = __fmaf_rn(-c1, iz, c0);
-                if (d >= 0.0f && d <= 1.0f) {
-                    const unsigned d24 = (unsigned)__float2int_rn(__fmul_rn(d, 16777215.0f));
-                    if (d24 < kDepthMax)
-                        smem_min64(&keys[s * kTilePix + pidx], ((unsigned long long)d24 << 32) | tri);
-                }
+                const unsigned key = depth_key(iz, c0, c1, local);
+                if (key != kKeyEmpty32) atomicMin(&z[s * kTilePix + pidx], key);
             }
         }
     }
 }
 
-// Rasterise the `qn` queued triangles into the tile's visibility buffer: triangles whose bbox∩tile is at most
-// kSmallPix pixels take one thread each, the others are deferred to one warp each.  Called by all threads.
-template <typename I>
-__device__ __forceinline__ void process_queue(const int* queue, int qn, int* medq, int* med_count,
-                                              const int4* __restrict__ img_recs, unsigned long long* keys,
-                                              int x_lo, int x_hi, int y_lo, int y_hi, float c0, float c1) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int k = tid; k < qn; k += kRasterThreads) {
-        const unsigned tri = (unsigned)queue[k];
-        const int4* r = img_recs + 3 * (size_t)tri;
-        const TriGeom g = unpack_geom(r[0], r[1], r[2]);
-        int bx0, bx1, by0, by1;
-        tri_bbox(g, x_lo, x_hi, y_lo, y_hi, bx0, bx1, by0, by1);
-        const int npix = (bx1 - bx0 + 1) * (by1 - by0 + 1);
-        if (bx0 > bx1 || by0 > by1) continue;
-        if (npix <= kSmallPix)
-            raster_tri<I>(g, tri, bx0, bx1, by0, by1, 0, 1, keys, x_lo, y_lo, c0, c1);
-        else
-            medq[atomicAdd(med_count, 1)] = (int)tri;
-    }
-    __syncthreads();
-    const int mn = *med_count;
-    for (int k = warp; k < mn; k += kRasterThreads / 32) {
-        const unsigned tri = (unsigned)medq[k];
-        const int4* r = img_recs + 3 * (size_t)tri;
-        const TriGeom g = unpack_geom(r[0], r[1], r[2]);
-        int bx0, bx1, by0, by1;
-        tri_bbox(g, x_lo, x_hi, y_lo, y_hi, bx0, bx1, by0, by1);
-        raster_tri<I>(g, tri, bx0, bx1, by0, by1, lane, 32, keys, x_lo, y_lo, c0, c1);
-    }
-    __syncthreads();
-    if (tid == 0) *med_count = 0;
-    __syncthreads();
-}
+// per-bin constants every phase needs
+struct BinCtx {
+    int x_lo, y_lo, x_hi, y_hi;      // inclusive pixel bounds (clipped to the image)
+    float c0, c1;
+    const int4* img_recs;
+};
 
-// Binned triangles (int32-exact), flattened so that lanes stay busy: each thread stages one queued triangle
-// (edge equations relative to its clipped bbox origin, depth plane, id) in shared memory and lists the bbox
-// pixels it must visit; the warp then walks the concatenated (triangle, pixel) items of its 32 triangles, 32 per
-// step, so a 1-pixel triangle and a 16-pixel triangle in the same warp cost 17 items, not 2 x 16.
-// Triangles with more than kSmallPix bbox pixels take the warp-per-triangle path.
-constexpr int kTriStride = 20;   // words per staged triangle (16 used; 80 B keeps LDS.128 aligned and conflict-free)
-
-constexpr size_t kRasterSmemBytes = (size_t)kTilePix * 32 + sizeof(int) * 2 * kQueueCap +
-                                    sizeof(int) * kRasterThreads * kTriStride + sizeof(unsigned short) * kRasterThreads * kSmallPix;
-
-__device__ __forceinline__ void process_queue_flat(const int* queue, int qn, int* medq, int* med_count,
-                                                   const int4* __restrict__ img_recs, unsigned long long* keys,
-                                                   int* s_tri, unsigned short* s_items,
-                                                   int x_lo, int x_hi, int y_lo, int y_hi, float c0, float c1
-                                                   RAC_PHASE_ARGS) {
+// ---------------------------------------------------------------------------------------------
+// coverage of one batch: ids[0..n), n <= kBatch, local ids first_local .. first_local + n - 1 (thread = triangle)
+// ---------------------------------------------------------------------------------------------
+// Binned triangles (int32-exact) are flattened so that lanes stay busy: each thread stages its triangle (edge
+// equations relative to its clipped bbox origin, depth plane, id) in shared memory and lists the bbox pixels it must
+// visit; the warp then walks the concatenated (triangle, pixel) items of its 32 triangles, 32 per step, so a 1-pixel
+// triangle and a 16-pixel triangle in the same warp cost 17 items, not 2 x 16.  Triangles with more than kSmallPix
+// bbox pixels (and every LARGE one: int64 edge functions) take the warp-per-triangle path.  Called by all threads.
+template <bool LARGE>
+__device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, const BinCtx& bc, const int* ids, int n,
+                                              unsigned first_local RAC_PHASE_ARGS) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int SX[4] = {96, 224, 32, 160};
     constexpr int SY[4] = {32, 96, 160, 224};
-    unsigned short* items = s_items + warp * (32 * kSmallPix);
-    for (int qb = 0; qb < qn; qb += kRasterThreads) {
-        const int k = qb + tid;
-        int n = 0, w = 0, h = 0;
-        if (k < qn) {
-            const unsigned tri = (unsigned)queue[k];
-            const int4* r = img_recs + 3 * (size_t)tri;
-            const int4 q0 = r[0], q1 = r[1], q2 = r[2];
-            const TriGeom g = unpack_geom(q0, q1, q2);
-            int bx0, bx1, by0, by1;
-            tri_bbox(g, x_lo, x_hi, y_lo, y_hi, bx0, bx1, by0, by1);
-            if (bx0 <= bx1 && by0 <= by1) {
-                w = bx1 - bx0 + 1; h = by1 - by0 + 1;
-                if (w * h <= kSmallPix) {
-                    n = w * h;
-                    const int dx0 = g.X1 - g.X0, dy0 = g.Y1 - g.Y0;
-                    const int dx1 = g.X2 - g.X1, dy1 = g.Y2 - g.Y1;
-                    const int dx2 = g.X0 - g.X2, dy2 = g.Y0 - g.Y2;
-                    const int b0 = (dy0 < 0 || (dy0 == 0 && dx0 > 0)) ? 0 : -1;
-                    const int b1 = (dy1 < 0 || (dy1 == 0 && dx1 > 0)) ? 0 : -1;
-                    const int b2 = (dy2 < 0 || (dy2 == 0 && dx2 > 0)) ? 0 : -1;
-                    const int ox = bx0 * kSubpix, oy = by0 * kSubpix;
-                    int4* slot = reinterpret_cast<int4*>(s_tri + tid * kTriStride);
-                    const int C0 = dx0 * (oy - g.Y0) - dy0 * (ox - g.X0) + b0;
-                    const int C1 = dx1 * (oy - g.Y1) - dy1 * (ox - g.X1) + b1;
-                    const int C2 = dx2 * (oy - g.Y2) - dy2 * (ox - g.X2) + b2;
-                    slot[0] = make_int4(-dy0, dx0, C0, -dy1);
-                    slot[1] = make_int4(dx1, C1, -dy2, dx2);
-                    slot[2] = make_int4(C2, ox - g.X0, oy - g.Y0, __float_as_int(g.gx));
-                    slot[3] = make_int4(__float_as_int(g.gy), __float_as_int(g.iz0), (int)tri,
-                                        (by0 - y_lo) * kTileW + (bx0 - x_lo));
-                } else {
-                    medq[atomicAdd(med_count, 1)] = (int)tri;
-                }
+    unsigned short* items = sm.items + warp * (32 * kSmallPix);
+    int nit = 0, w = 0, h = 0;
+    if (tid < n) {
+        const unsigned tri = (unsigned)ids[tid];
+        const unsigned local = first_local + (unsigned)tid;
+        sm.slots[local - 1u] = tri;
+        const int4* r = bc.img_recs + 3 * (size_t)tri;
+        const int4 q0 = r[0], q1 = r[1], q2 = r[2];
+        const TriGeom g = unpack_geom(q0, q1, q2);
+        int bx0, bx1, by0, by1;
+        tri_bbox(g, bc.x_lo, bc.x_hi, bc.y_lo, bc.y_hi, bx0, bx1, by0, by1);
+        if (bx0 <= bx1 && by0 <= by1) {
+            w = bx1 - bx0 + 1; h = by1 - by0 + 1;
+            if (!LARGE && w * h <= kSmallPix) {
+                nit = w * h;
+                const int dx0 = g.X1 - g.X0, dy0 = g.Y1 - g.Y0;
+                const int dx1 = g.X2 - g.X1, dy1 = g.Y2 - g.Y1;
+                const int dx2 = g.X0 - g.X2, dy2 = g.Y0 - g.Y2;
+                const int b0 = (dy0 < 0 || (dy0 == 0 && dx0 > 0)) ? 0 : -1;
+                const int b1 = (dy1 < 0 || (dy1 == 0 && dx1 > 0)) ? 0 : -1;
+                const int b2 = (dy2 < 0 || (dy2 == 0 && dx2 > 0)) ? 0 : -1;
+                const int ox = bx0 * kSubpix, oy = by0 * kSubpix;
+                int4* slot = reinterpret_cast<int4*>(sm.tri + tid * kTriStride);
+                const int C0 = dx0 * (oy - g.Y0) - dy0 * (ox - g.X0) + b0;
+                const int C1 = dx1 * (oy - g.Y1) - dy1 * (ox - g.X1) + b1;
+                const int C2 = dx2 * (oy - g.Y2) - dy2 * (ox - g.X2) + b2;
+                slot[0] = make_int4(-dy0, dx0, C0, -dy1);
+                slot[1] = make_int4(dx1, C1, -dy2, dx2);
+                slot[2] = make_int4(C2, ox - g.X0, oy - g.Y0, __float_as_int(g.gx));
+                slot[3] = make_int4(__float_as_int(g.gy), __float_as_int(g.iz0), (int)local,
+                                    (by0 - bc.y_lo) * kTileW + (bx0 - bc.x_lo));
+            } else {
+                sm.medq[atomicAdd(med_count, 1)] = tid;
             }
         }
-        int incl = n;
+    }
+    if (!LARGE) {
+        int incl = nit;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int v = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += v;
         }
         const int total = __shfl_sync(0xffffffffu, incl, 31);
-        if (n) {
-            int idx = incl - n;
+        if (nit) {
+            int idx = incl - nit;
             for (int dy = 0; dy < h; ++dy)
                 for (int dx = 0; dx < w; ++dx) items[idx++] = (unsigned short)(lane | (dx << 5) | (dy << 9));
         }
         __syncwarp();
+        const float c0 = bc.c0, c1 = bc.c1;
         for (int j = lane; j < total; j += 32) {
             const int code = items[j];
             const int dxp = (code >> 5) & 15, dyp = code >> 9;
-            const int4* slot = reinterpret_cast<const int4*>(s_tri + ((warp << 5) + (code & 31)) * kTriStride);
+            const int4* slot = reinterpret_cast<const int4*>(sm.tri + ((warp << 5) + (code & 31)) * kTriStride);
             const int4 a = slot[0], b = slot[1], c = slot[2], d = slot[3];
             const int sx = dxp * kSubpix, sy = dyp * kSubpix;
             const float gx = __int_as_float(c.w), gy = __int_as_float(d.x), iz0 = __int_as_float(d.y);
@@ -213,28 +206,24 @@ __device__ __forceinline__ void process_queue_flat(const int* queue, int qn, int
                 if ((e0 | e1 | e2) >= 0) {
                     const float fxr = (float)(c.y + ux), fyr = (float)(c.z + uy);
                     const float iz = __fmaf_rn(gy, fyr, __fmaf_rn(gx, fxr, iz0));
-                    const float dd = __fmaf_rn(-c1, iz, c0);
-                    if (dd >= 0.0f && dd <= 1.0f) {
-                        const unsigned d24 = (unsigned)__float2int_rn(__fmul_rn(dd, 16777215.0f));
-                        if (d24 < kDepthMax)
-                            smem_min64(&keys[s * kTilePix + pidx], ((unsigned long long)d24 << 32) | (unsigned)d.z);
-                    }
+                    const unsigned key = depth_key(iz, c0, c1, (unsigned)d.z);
+                    if (key != kKeyEmpty32) atomicMin(&sm.z[s * kTilePix + pidx], key);
                 }
             }
         }
-        __syncwarp();
     }
     RAC_PHASE(2);
     __syncthreads();
     RAC_PHASE(3);
     const int mn = *med_count;
-    for (int k = warp; k < mn; k += kRasterThreads / 32) {
-        const unsigned tri = (unsigned)medq[k];
-        const int4* r = img_recs + 3 * (size_t)tri;
+    for (int k = warp; k < mn; k += kRasterWarpsN) {
+        const int t = sm.medq[k];
+        const int4* r = bc.img_recs + 3 * (size_t)(unsigned)ids[t];
         const TriGeom g = unpack_geom(r[0], r[1], r[2]);
         int bx0, bx1, by0, by1;
-        tri_bbox(g, x_lo, x_hi, y_lo, y_hi, bx0, bx1, by0, by1);
-        raster_tri<int>(g, tri, bx0, bx1, by0, by1, lane, 32, keys, x_lo, y_lo, c0, c1);
+        tri_bbox(g, bc.x_lo, bc.x_hi, bc.y_lo, bc.y_hi, bx0, bx1, by0, by1);
+        raster_tri_warp<typename std::conditional<LARGE, long long, int>::type>(
+            g, first_local + (unsigned)t, bx0, bx1, by0, by1, lane, sm.z, bc.x_lo, bc.y_lo, bc.c0, bc.c1);
     }
     __syncthreads();
     RAC_PHASE(4);
@@ -242,231 +231,290 @@ __device__ __forceinline__ void process_queue_flat(const int* queue, int qn, int
     __syncthreads();
 }
 
+// ---------------------------------------------------------------------------------------------
+// resolve / commit
+// ---------------------------------------------------------------------------------------------
 struct TileAcc {
     unsigned qmax, dcount;
     float dmax;
     double dsum, dsumsq;
 };
 
-// Everything one CTA does for tile `tile` of image `b`: gather -> coverage/depth -> shade/resolve -> RGBA8 + depth
-// stores -> per-image accumulators.  smem_raw: keys [4][kTilePix] u64, queue [kQueueCap], medq [kQueueCap],
-// staged triangles [kRasterThreads][kTriStride], item lists [8][32*kSmallPix] u16.
-__device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl, unsigned* s_scan,
+// Flattened shading.  R1: every pixel finds the distinct uncommitted winners among its 4 samples and lists one
+// (pixel, representative sample) item per distinct triangle; R2: the items are shaded 256 at a time (no lane idles on
+// background or waits for a neighbour's 4-triangle edge pixel); R3 (FINAL): every pixel averages its samples' colours
+// through the representatives / the committed colours and stores RGBA8 + depth.
+// FINAL = false (commit): R2 parks the colours in the CTA's global scratch and clears the ids; no R3.
+// Called by all threads; q_count is a zeroed shared counter (left zeroed).
+template <bool FINAL>
+__device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const BinCtx& bc,
+                                            unsigned* __restrict__ scratch_col, const ShadeCtx* s_sc,
+                                            const SceneConsts& S, unsigned* __restrict__ rgba_out,
+                                            float* __restrict__ depth_out, size_t img_pix, int W, TileAcc& acc
+                                            RAC_PHASE_ARGS) {
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int tw = bc.x_hi - bc.x_lo + 1, th = bc.y_hi - bc.y_lo + 1;
+    unsigned short* sitems = sm.items;   // [4 * kTilePix] of the 4096: free between batches (the queue is NOT: a commit runs mid-queue)
+    unsigned* cols = reinterpret_cast<unsigned*>(sm.tri);   // [4 * kTilePix] colour of each representative sample (staging area is idle here)
+    constexpr int kPer = kTilePix / kRasterThreads;
+    // R1.  Nothing is kept in registers across the shading pass: R3 re-derives the representatives from the keys.
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) {
+        const int p = tid + i * kRasterThreads;
+        const int lx = p & (kTileW - 1), ly = p / kTileW;
+        const bool inb = lx < tw && ly < th;
+        unsigned k[4];
+#pragma unroll
+        for (int s = 0; s < 4; ++s) k[s] = inb ? sm.z[s * kTilePix + p] : kKeyEmpty32;
+        unsigned fresh = 0;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            if (k[s] == kKeyEmpty32 || (k[s] & 0xFFu) == 0u) continue;
+            bool first = true;
+#pragma unroll
+            for (int j = s - 1; j >= 0; --j)
+                if (((k[j] ^ k[s]) & 0xFFu) == 0u) first = false;      // (ids are 1..254: 0 = committed, 0xFF = empty key)
+            if (first) fresh |= 1u << s;
+        }
+        // append this pixel's items (warp-aggregated)
+        const int c = __popc(fresh);
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        int base = 0;
+        if (lane == 31 && incl) base = atomicAdd(q_count, incl);
+        base = __shfl_sync(0xffffffffu, base, 31) + incl - c;
+#pragma unroll
+        for (int s = 0; s < 4; ++s)
+            if (fresh & (1u << s)) sitems[base++] = (unsigned short)(p | (s << 10));
+    }
+    RAC_PHASE(6);
+    __syncthreads();
+    RAC_PHASE(7);
+    const int nitems = *q_count;
+    if (nitems > 0) {       // CTA-uniform
+        const ShadeCtx sc = *s_sc;      // built once per bin by thread 0, long before this point
+        for (int it = tid; it < nitems; it += kRasterThreads) {
+            const int code = sitems[it];
+            const int p = code & 1023, s = code >> 10;
+            const unsigned key = sm.z[s * kTilePix + p];
+            const unsigned tri = sm.slots[(key & 0xFFu) - 1u];
+            const unsigned col = shade(sc, bc.img_recs + 3 * (size_t)tri, tri, bc.x_lo + (p & (kTileW - 1)), bc.y_lo + p / kTileW);
+            if (FINAL) {
+                cols[s * kTilePix + p] = col;      // R3 finds it through the representative index
+            } else {
+                // commit: every sample of this pixel won by the same triangle gets the colour; the ids are cleared
+#pragma unroll
+                for (int s2 = 0; s2 < 4; ++s2) {
+                    const unsigned k2 = sm.z[s2 * kTilePix + p];
+                    if (s2 >= s && k2 != kKeyEmpty32 && ((k2 ^ key) & 0xFFu) == 0u) {
+                        scratch_col[s2 * kTilePix + p] = col;
+                        sm.z[s2 * kTilePix + p] = k2 & ~0xFFu;
+                    }
+                }
+            }
+        }
+    }
+    RAC_PHASE(8);
+    __syncthreads();
+    RAC_PHASE(9);
+    if (tid == 0) *q_count = 0;
+    if (!FINAL) { __syncthreads(); return; }
+#pragma unroll
+    for (int i = 0; i < kPer; ++i) {
+        const int p = tid + i * kRasterThreads;
+        const int lx = p & (kTileW - 1), ly = p / kTileW;
+        if (lx >= tw || ly >= th) continue;
+        unsigned k[4];
+#pragma unroll
+        for (int s = 0; s < 4; ++s) k[s] = sm.z[s * kTilePix + p];
+        unsigned sum_r = 0, sum_g = 0, sum_b = 0, sum_a = 0;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            if (k[s] == kKeyEmpty32) continue;
+            unsigned col;
+            if ((k[s] & 0xFFu) == 0u) {
+                col = __ldcg(scratch_col + s * kTilePix + p);          // committed earlier
+            } else {
+                int rep = s;
+#pragma unroll
+                for (int j = s - 1; j >= 0; --j)
+                    if (((k[j] ^ k[s]) & 0xFFu) == 0u) rep = j;
+                col = cols[rep * kTilePix + p];
+            }
+            sum_r += col & 0xFFu; sum_g += (col >> 8) & 0xFFu;
+            sum_b += (col >> 16) & 0xFFu; sum_a += col >> 24;
+        }
+        const unsigned r8 = (sum_r + 2u) >> 2, g8 = (sum_g + 2u) >> 2, b8 = (sum_b + 2u) >> 2, a8 = (sum_a + 2u) >> 2;
+        const size_t o = img_pix + (size_t)(bc.y_lo + ly) * W + (bc.x_lo + lx);
+        rgba_out[o] = r8 | (g8 << 8) | (b8 << 16) | (a8 << 24);
+        float depth = 0.0f;
+        if (k[0] != kKeyEmpty32) depth = depth_readback(k[0] >> 8, S);
+        depth_out[o] = depth;
+        acc.qmax = max(acc.qmax, max(r8, max(g8, b8)));
+        acc.dmax = fmaxf(acc.dmax, depth);
+        if (depth > 0.01f) { acc.dcount++; acc.dsum += (double)depth; acc.dsumsq += (double)depth * (double)depth; }
+    }
+}
+
+// commit (rare: more than 254 triangles in a bin) — out of line, so that the hot path carries one copy of the resolve
+__device__ __noinline__ void commit_bin(RasterSmem& sm, int* q_count, const BinCtx& bc, unsigned* __restrict__ scratch_col,
+                                        const ShadeCtx* s_sc, const SceneConsts& S RAC_PHASE_ARGS) {
+    TileAcc dummy;
+    resolve_bin<false>(sm, q_count, bc, scratch_col, s_sc, S, nullptr, nullptr, 0, 0, dummy RAC_PHASE_PASS);
+}
+
+// ---------------------------------------------------------------------------------------------
+// one bin, start to finish
+// ---------------------------------------------------------------------------------------------
+// s_ctl: [0] resolve item count, [1] medium-triangle count (both zero on entry and on exit);
+// s_scan: [4 * kRasterThreads + 8] descriptor counts / scan / offsets / large counts / warp sums.
+__device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned* s_scan, ShadeCtx* s_sc, unsigned* __restrict__ scratch_col,
                                             const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids,
                                             int uniform_mesh, const float* __restrict__ T_CO, const float* __restrict__ K,
                                             int W, int H, int maxT, const TileGrid& tg, const SceneConsts& S,
-                                            ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
-                                            const int4* __restrict__ recs, const unsigned* __restrict__ desc,
-                                            const unsigned char* __restrict__ refs, unsigned* __restrict__ rgba_out,
-                                            float* __restrict__ depth_out, int b, int tile RAC_PHASE_ARGS) {
-    unsigned long long* keys = reinterpret_cast<unsigned long long*>(smem_raw);           // [4][kTilePix]
-    int* queue = reinterpret_cast<int*>(keys + 4 * kTilePix);                              // [kQueueCap]
-    int* medq = queue + kQueueCap;                                                         // [kQueueCap]
-    int* s_tri = medq + kQueueCap;                                                         // [kRasterThreads][kTriStride]
-    unsigned short* s_items = reinterpret_cast<unsigned short*>(s_tri + kRasterThreads * kTriStride);  // [8][32*kSmallPix]
+                                            ImgStats* __restrict__ stats, const unsigned* __restrict__ large_cnt,
+                                            const unsigned* __restrict__ large_tri, const int4* __restrict__ recs,
+                                            const unsigned* __restrict__ desc, const unsigned char* __restrict__ refs,
+                                            unsigned* __restrict__ rgba_out, float* __restrict__ depth_out,
+                                            int b, int tile RAC_PHASE_ARGS) {
     int* q_count = s_ctl, *med_count = s_ctl + 1;
-    unsigned* s_dcnt = s_scan;                      // [kRasterThreads] descriptor counts
+    unsigned* s_dcnt = s_scan;                      // [kRasterThreads] descriptor counts (large pass: per-CTA counts)
     unsigned* s_dscan = s_scan + kRasterThreads;    // [kRasterThreads] exclusive scan
     unsigned* s_doff = s_scan + 2 * kRasterThreads; // [kRasterThreads] offset into the ref region
     unsigned* s_wsum = s_scan + 3 * kRasterThreads; // [8]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tx = tile % tg.ntx, ty = tile / tg.ntx;
-    const int x_lo = tx * kTileW, y_lo = ty * kTileH;
-    const int x_hi = min(x_lo + kTileW, W) - 1, y_hi = min(y_lo + kTileH, H) - 1;
+    BinCtx bc;
+    bc.x_lo = (tile % tg.ntx) * kTileW; bc.y_lo = (tile / tg.ntx) * kTileH;
+    bc.x_hi = min(bc.x_lo + kTileW, W) - 1; bc.y_hi = min(bc.y_lo + kTileH, H) - 1;
+    bc.c0 = S.c0; bc.c1 = S.c1;
+    bc.img_recs = recs + 3 * (size_t)b * maxT;
     const MeshDev& mesh = table[mesh_ids ? mesh_ids[b] : uniform_mesh];
-    const int4* img_recs = recs + 3 * (size_t)b * maxT;
-    const unsigned n_large = stats[b].nlarge;   // written by setup_kernel (previous launch)
-    const int ncta = tg.binned ? (mesh.T + kSetupThreads - 1) / kSetupThreads : 0;
-
-    if (tid == 0) { *q_count = 0; *med_count = 0; }
-    bool inited = false;   // CTA-uniform
+    const int ncta = (mesh.T + kSetupThreads - 1) / kSetupThreads;
+    const size_t img_pix = (size_t)b * W * H;
+    {
+        uint4* z4 = reinterpret_cast<uint4*>(sm.z);
+        const uint4 e = make_uint4(kKeyEmpty32, kKeyEmpty32, kKeyEmpty32, kKeyEmpty32);
+#pragma unroll
+        for (int i = 0; i < kTilePix / kRasterThreads; ++i) z4[tid + i * kRasterThreads] = e;
+    }
+    int nslots = 0;           // local ids handed out since the last commit (CTA-uniform)
+    if (tid == kRasterThreads - 1) {     // the shading context of this (image, mesh): consumed after several barriers
+        const CamPose cam = load_campose(T_CO, K, b);
+        *s_sc = make_shade_ctx(mesh, cam, S);
+    }
+    const unsigned n_large_img = stats[b].nlarge;     // written by setup_kernel (previous launch)
+    // coverage of sm.queue[0..qn) in batches of <= kBatch local ids; commits when the ids run out
+    auto run_batches = [&](int qn, auto large_tag) {
+        constexpr bool LARGE = decltype(large_tag)::value;
+        for (int qb = 0; qb < qn; qb += kBatch) {
+            const int n = min(kBatch, qn - qb);
+            if (nslots + n > kBatch) {
+                commit_bin(sm, q_count, bc, scratch_col, s_sc, S RAC_PHASE_PASS);
+                nslots = 0;
+            }
+            process_batch<LARGE>(sm, med_count, bc, sm.queue + qb, n, (unsigned)nslots + 1u RAC_PHASE_PASS);
+            nslots += n;
+        }
+    };
     __syncthreads();
 
-    // ---- binned triangles: descriptors of this tile, kRasterThreads at a time ----
-    const unsigned* dtile = desc + ((size_t)b * tg.nt + tile) * tg.ncta_max;
-    for (int dbase = 0; dbase < ncta; dbase += kRasterThreads) {
-        const int j = dbase + tid;
-        const unsigned d = j < ncta ? dtile[j] : 0u;
-        const unsigned c = d & 0xFFFFu;
-        unsigned incl = c;
+    // ---- binned triangles: descriptors of this bin, kRasterThreads at a time ----
+    if (tg.binned) {
+        const unsigned* dtile = desc + ((size_t)b * tg.nt + tile) * tg.ncta_max;
+        for (int dbase = 0; dbase < ncta; dbase += kRasterThreads) {
+            const int j = dbase + tid;
+            const unsigned d = j < ncta ? dtile[j] : 0u;
+            const unsigned c = d & 0xFFFFu;
+            unsigned incl = c;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += v;
-        }
-        if (lane == 31) s_wsum[warp] = incl;
-        __syncthreads();
-        unsigned wbase = 0, total = 0;
-#pragma unroll
-        for (int w = 0; w < kRasterThreads / 32; ++w) {
-            const unsigned v = s_wsum[w];
-            if (w < warp) wbase += v;
-            total += v;
-        }
-        s_dcnt[tid] = c; s_dscan[tid] = wbase + incl - c; s_doff[tid] = d >> 16;
-        __syncthreads();
-        const int nd = min(kRasterThreads, ncta - dbase);
-        for (unsigned base = 0; base < total; base += kQueueCap) {
-            // expand refs [base, base + kQueueCap) of this descriptor group into the queue, one warp per descriptor
-            for (int jj = warp; jj < nd; jj += kRasterThreads / 32) {
-                const unsigned cj = s_dcnt[jj];
-                if (cj == 0) continue;
-                const unsigned sj = s_dscan[jj];
-                const unsigned lo = max(sj, base), hi = min(sj + cj, base + (unsigned)kQueueCap);
-                const unsigned char* region = refs + (((size_t)b * tg.ncta_max + dbase + jj) << 10) + s_doff[jj];
-                for (unsigned k = lo + lane; k < hi; k += 32)
-                    queue[k - base] = (dbase + jj) * kSetupThreads + (int)region[k - sj];
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
             }
-            if (!inited) {
-                for (int k = tid; k < 4 * kTilePix; k += kRasterThreads) keys[k] = kKeyEmpty;
-                inited = true;
-            }
+            if (lane == 31) s_wsum[warp] = incl;
             __syncthreads();
-            RAC_PHASE(1);
-            const int qn = (int)min((unsigned)kQueueCap, total - base);
-            process_queue_flat(queue, qn, medq, med_count, img_recs, keys, s_tri, s_items, x_lo, x_hi, y_lo, y_hi, S.c0, S.c1 RAC_PHASE_PASS);
+            unsigned wbase = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < kRasterWarpsN; ++w) {
+                const unsigned v = s_wsum[w];
+                if (w < warp) wbase += v;
+                total += v;
+            }
+            s_dcnt[tid] = c; s_dscan[tid] = wbase + incl - c; s_doff[tid] = d >> 16;
+            __syncthreads();
+            const int nd = min(kRasterThreads, ncta - dbase);
+            for (unsigned base = 0; base < total; base += kQueueCap) {
+                // expand refs [base, base + kQueueCap) of this descriptor group into the queue, one warp per descriptor
+                for (int jj = warp; jj < nd; jj += kRasterWarpsN) {
+                    const unsigned cj = s_dcnt[jj];
+                    if (cj == 0) continue;
+                    const unsigned sj = s_dscan[jj];
+                    const unsigned lo = max(sj, base), hi = min(sj + cj, base + (unsigned)kQueueCap);
+                    const unsigned char* region = refs + (((size_t)b * tg.ncta_max + dbase + jj) << 10) + s_doff[jj];
+                    for (unsigned k = lo + lane; k < hi; k += 32)
+                        sm.queue[k - base] = (dbase + jj) * kSetupThreads + (int)region[k - sj];
+                }
+                __syncthreads();
+                RAC_PHASE(1);
+                run_batches((int)min((unsigned)kQueueCap, total - base), std::false_type());
+            }
         }
     }
 
-    // ---- large triangles: every tile scans the image's large list ----
-    for (unsigned base = 0; base < n_large; base += kRasterThreads) {
-        const unsigned i = base + tid;
-        if (i < n_large) {
-            const unsigned tri = large_tri[(size_t)b * maxT + i];
-            const int4* r = img_recs + 3 * (size_t)tri;
-            const int4 q0 = r[0], q1 = r[1];
-            const int xmin = min(q0.x, min(q0.z, q1.x)), xmax = max(q0.x, max(q0.z, q1.x));
-            const int ymin = min(q0.y, min(q0.w, q1.y)), ymax = max(q0.y, max(q0.w, q1.y));
-            if (ceil_div256(xmin - 224) <= x_hi && floor_div256(xmax - 32) >= x_lo &&
-                ceil_div256(ymin - 224) <= y_hi && floor_div256(ymax - 32) >= y_lo)
-                queue[atomicAdd(q_count, 1)] = (int)tri;
-        }
+    // ---- large triangles: every bin scans the image's large list, per setup CTA and in triangle order ----
+    for (int dbase = 0; n_large_img != 0u && dbase < ncta; dbase += kRasterThreads) {
+        s_dcnt[tid] = (dbase + tid < ncta) ? large_cnt[(size_t)b * tg.ncta_max + dbase + tid] : 0u;
         __syncthreads();
-        const int qn = *q_count;
-        const bool last = base + kRasterThreads >= n_large;
-        if (qn > 0 && (last || qn > kQueueCap - kRasterThreads)) {
-            if (!inited) {
-                for (int k = tid; k < 4 * kTilePix; k += kRasterThreads) keys[k] = kKeyEmpty;
-                inited = true;
-                __syncthreads();
+        const int nd = min(kRasterThreads, ncta - dbase);
+        int qn = 0;
+        for (int jj = 0; jj < nd; ++jj) {
+            const int cj = (int)s_dcnt[jj];
+            if (cj == 0) continue;                 // CTA-uniform
+            const unsigned* lst = large_tri + (size_t)b * maxT + (size_t)(dbase + jj) * kSetupThreads;
+            bool accept = false;
+            unsigned tri = 0;
+            if (tid < cj) {                        // cj <= kSetupThreads == kRasterThreads
+                tri = lst[tid];
+                const int4* r = bc.img_recs + 3 * (size_t)tri;
+                const int4 q0 = r[0], q1 = r[1];
+                const int xmin = min(q0.x, min(q0.z, q1.x)), xmax = max(q0.x, max(q0.z, q1.x));
+                const int ymin = min(q0.y, min(q0.w, q1.y)), ymax = max(q0.y, max(q0.w, q1.y));
+                accept = ceil_div256(xmin - 224) <= bc.x_hi && floor_div256(xmax - 32) >= bc.x_lo &&
+                         ceil_div256(ymin - 224) <= bc.y_hi && floor_div256(ymax - 32) >= bc.y_lo;
             }
-            process_queue<long long>(queue, qn, medq, med_count, img_recs, keys, x_lo, x_hi, y_lo, y_hi, S.c0, S.c1);
-            if (tid == 0) *q_count = 0;
+            const unsigned am = __ballot_sync(0xffffffffu, accept);
+            if (lane == 0) s_wsum[warp] = (unsigned)__popc(am);
             __syncthreads();
+            unsigned wbase = 0, total = 0;
+#pragma unroll
+            for (int w = 0; w < kRasterWarpsN; ++w) {
+                const unsigned v = s_wsum[w];
+                if (w < warp) wbase += v;
+                total += v;
+            }
+            if (accept) sm.queue[qn + (int)wbase + __popc(am & ((1u << lane) - 1u))] = (int)tri;
+            qn += (int)total;
+            __syncthreads();
+            if (qn > kQueueCap - kRasterThreads) { run_batches(qn, std::true_type()); qn = 0; }
         }
+        if (qn > 0) run_batches(qn, std::true_type());
+        __syncthreads();
     }
 
     RAC_PHASE(5);
     // ---- resolve + shade + write, and per-image accumulators ----
-    const int tw = x_hi - x_lo + 1, th = y_hi - y_lo + 1;
     TileAcc acc;
     acc.qmax = 0; acc.dcount = 0; acc.dmax = 0.0f; acc.dsum = 0.0; acc.dsumsq = 0.0;
-    const size_t img_pix = (size_t)b * W * H;
-    if (!inited) {
-        for (int p = tid; p < kTilePix; p += kRasterThreads) {
-            const int lx = p & (kTileW - 1), ly = p / kTileW;
-            if (lx < tw && ly < th) {
-                const size_t o = img_pix + (size_t)(y_lo + ly) * W + (x_lo + lx);
-                rgba_out[o] = 0u;
-                depth_out[o] = 0.0f;
-            }
-        }
-    } else {
-        // Flattened shading.  R1: every pixel finds the distinct triangles among its 4 samples and lists one
-        // (pixel, sample) item per distinct triangle; R2: the items are shaded 256 at a time (no lane idles on
-        // background or waits for a neighbour's 4-triangle edge pixel) and the RGBA8 colour replaces the triangle
-        // id in the key's low word; R3: every pixel sums its samples' colours through the representatives.
-        const CamPose cam = load_campose(T_CO, K, b);
-        const ShadeCtx sc = make_shade_ctx(mesh, cam, S);
-        unsigned short* sitems = reinterpret_cast<unsigned short*>(queue);   // [4 * kTilePix] aliases queue + medq
-        unsigned* key_lo = reinterpret_cast<unsigned*>(keys);
-        constexpr int kPer = kTilePix / kRasterThreads;
-        unsigned info[kPer];     // per pixel: rep[s] (2 bits each) | covered mask << 8
-        unsigned d24s[kPer];     // depth of sample 0
-#pragma unroll
-        for (int i = 0; i < kPer; ++i) {
-            const int p = tid + i * kRasterThreads;
-            const int lx = p & (kTileW - 1), ly = p / kTileW;
-            unsigned long long k[4];
-#pragma unroll
-            for (int sidx = 0; sidx < 4; ++sidx)
-                k[sidx] = (lx < tw && ly < th) ? keys[sidx * kTilePix + p] : kKeyEmpty;
-            unsigned reps = 0, mask = 0, fresh = 0;
-#pragma unroll
-            for (int sidx = 0; sidx < 4; ++sidx) {
-                if (k[sidx] != kKeyEmpty) {
-                    mask |= 1u << sidx;
-                    unsigned rep = sidx;
-#pragma unroll
-                    for (int j = sidx - 1; j >= 0; --j)
-                        if (k[j] != kKeyEmpty && (unsigned)k[j] == (unsigned)k[sidx]) rep = j;
-                    reps |= rep << (2 * sidx);
-                    if (rep == (unsigned)sidx) fresh |= 1u << sidx;
-                }
-            }
-            info[i] = reps | (mask << 8);
-            d24s[i] = (mask & 1u) ? (unsigned)(k[0] >> 32) : kDepthMax;
-            // append this pixel's items (warp-aggregated)
-            const int c = __popc(fresh);
-            int incl = c;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += v;
-            }
-            int base = 0;
-            if (lane == 31 && incl) base = atomicAdd(q_count, incl);
-            base = __shfl_sync(0xffffffffu, base, 31) + incl - c;
-#pragma unroll
-            for (int sidx = 0; sidx < 4; ++sidx)
-                if (fresh & (1u << sidx)) sitems[base++] = (unsigned short)(p | (sidx << 10));
-        }
-        RAC_PHASE(6);
-        __syncthreads();
-        RAC_PHASE(7);
-        const int nitems = *q_count;
-        for (int it = tid; it < nitems; it += kRasterThreads) {
-            const int code = sitems[it];
-            const int p = code & 1023, sidx = code >> 10;
-            const unsigned tri = key_lo[2 * (sidx * kTilePix + p)];
-            key_lo[2 * (sidx * kTilePix + p)] = shade(sc, img_recs + 3 * (size_t)tri, tri, x_lo + (p & (kTileW - 1)), y_lo + p / kTileW);
-        }
-        RAC_PHASE(8);
-        __syncthreads();
-        RAC_PHASE(9);
-        if (tid == 0) *q_count = 0;
-#pragma unroll
-        for (int i = 0; i < kPer; ++i) {
-            const int p = tid + i * kRasterThreads;
-            const int lx = p & (kTileW - 1), ly = p / kTileW;
-            if (lx >= tw || ly >= th) continue;
-            const unsigned mask = info[i] >> 8;
-            unsigned sum_r = 0, sum_g = 0, sum_b = 0, sum_a = 0;
-#pragma unroll
-            for (int sidx = 0; sidx < 4; ++sidx) {
-                if (mask & (1u << sidx)) {
-                    const unsigned rep = (info[i] >> (2 * sidx)) & 3u;
-                    const unsigned col = key_lo[2 * (rep * kTilePix + p)];
-                    sum_r += col & 0xFFu; sum_g += (col >> 8) & 0xFFu;
-                    sum_b += (col >> 16) & 0xFFu; sum_a += col >> 24;
-                }
-            }
-            const unsigned r8 = (sum_r + 2u) >> 2, g8 = (sum_g + 2u) >> 2, b8 = (sum_b + 2u) >> 2, a8 = (sum_a + 2u) >> 2;
-            const size_t o = img_pix + (size_t)(y_lo + ly) * W + (x_lo + lx);
-            rgba_out[o] = r8 | (g8 << 8) | (b8 << 16) | (a8 << 24);
-            float depth = 0.0f;
-            if (mask & 1u) depth = depth_readback(d24s[i], S);
-            depth_out[o] = depth;
-            acc.qmax = max(acc.qmax, max(r8, max(g8, b8)));
-            acc.dmax = fmaxf(acc.dmax, depth);
-            if (depth > 0.01f) { acc.dcount++; acc.dsum += (double)depth; acc.dsumsq += (double)depth * (double)depth; }
-        }
-    }
+    resolve_bin<true>(sm, q_count, bc, scratch_col, s_sc, S, rgba_out, depth_out, img_pix, W, acc RAC_PHASE_PASS);
     RAC_PHASE(10);
     // block reduction -> one atomic per accumulator per CTA
-    __shared__ double red_d[2][kRasterThreads / 32];
-    __shared__ unsigned red_u[3][kRasterThreads / 32];
+    __shared__ double red_d[2][kRasterWarpsN];
+    __shared__ unsigned red_u[3][kRasterWarpsN];
     acc.qmax = warp_max(acc.qmax);
     acc.dcount = (unsigned)__reduce_add_sync(0xffffffffu, acc.dcount);
     const unsigned dmax_bits = warp_max(__float_as_uint(acc.dmax));
@@ -479,7 +527,7 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
     if (tid == 0) {
         unsigned qm = 0, dc = 0, dm = 0;
         double a = 0, c = 0;
-        for (int w = 0; w < kRasterThreads / 32; ++w) {
+        for (int w = 0; w < kRasterWarpsN; ++w) {
             qm = max(qm, red_u[0][w]); dc += red_u[1][w]; dm = max(dm, red_u[2][w]);
             a += red_d[0][w]; c += red_d[1][w];
         }
@@ -490,51 +538,43 @@ __device__ __forceinline__ void raster_tile(unsigned char* smem_raw, int* s_ctl,
     }
 }
 
-// Persistent CTAs (SMs x resident CTAs) pop non-empty tiles from the work list setup_kernel built, image-major
-// through img_base (item r belongs to image b with img_base[b] <= r < img_base[b+1]).  The claim for the NEXT item
-// is issued before the current tile is rasterised, so the atomic's round trip to L2 is hidden behind the tile.
+// Persistent CTAs (SMs x resident CTAs) pop non-empty bins from the flat work list setup_kernel built.  The claim for
+// the NEXT item is issued before the current bin is rasterised, so the atomic's round trip to L2 hides behind the bin.
+// (kRasterRegs = 56: 4 CTAs/SM leave 8 K registers, one resident gt_norm CTA of 256 threads x 32 registers per SM.)
+constexpr int kRasterRegs = 56;
 __global__ void __maxnreg__(kRasterRegs)
 raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
               const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
-              SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_tri,
-              const int4* __restrict__ recs, const unsigned* __restrict__ desc, const unsigned char* __restrict__ refs,
-              WorkCtl* __restrict__ ctl, const unsigned* __restrict__ worklist, const unsigned* __restrict__ img_base,
-              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, int B) {
+              SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_cnt,
+              const unsigned* __restrict__ large_tri, const int4* __restrict__ recs, const unsigned* __restrict__ desc,
+              const unsigned char* __restrict__ refs, WorkCtl* __restrict__ ctl, const unsigned* __restrict__ worklist,
+              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, unsigned* __restrict__ scratch_col) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    RasterSmem& sm = *reinterpret_cast<RasterSmem*>(smem_raw);
     __shared__ int s_ctl[2];
     __shared__ unsigned s_item;
-    __shared__ unsigned s_scan[3 * kRasterThreads + kRasterThreads / 32];
-    const unsigned n_work = img_base[B];    // final: written by setup_kernel (previous launch)
+    __shared__ unsigned s_scan[3 * kRasterThreads + kRasterWarpsN];
+    __shared__ ShadeCtx s_sc;
+    const unsigned n_work = __ldcg(&ctl->n_work);    // final: written by setup_kernel (previous launch)
+    unsigned* my_scratch = scratch_col + (size_t)blockIdx.x * kScratchPerCta;
 #ifdef RAC_PHASE_TIMING
     WorkCtl* g_phase_ctl = ctl;
     long long g_phase_t = clock64();
 #endif
     RAC_TL(2);
-#ifdef RAC_PHASE_TIMING
-    if (threadIdx.x == 0) {      // late starters: CTAs that became resident more than 10 us after the first one
-        unsigned long long t;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-        if (t > g_tl[4] + 10000ull) atomicAdd(&g_tl[8], 1ull);
-    }
-#endif
-    if (threadIdx.x == 0) s_item = atomicAdd(&ctl->next, 1u);
+    if (threadIdx.x == 0) { s_item = atomicAdd(&ctl->next, 1u); s_ctl[0] = 0; s_ctl[1] = 0; }
     __syncthreads();
     for (;;) {
         const unsigned r = s_item;
         if (r >= n_work) break;
         unsigned r_next = 0;
-        if (threadIdx.x == 0) r_next = atomicAdd(&ctl->next, 1u);   // consumed after the tile
-        int lo = 0, hi = B;          // img_base[lo] <= r < img_base[hi]
-        while (hi - lo > 1) {
-            const int mid = (lo + hi) >> 1;
-            if (img_base[mid] <= r) lo = mid; else hi = mid;
-        }
-        const unsigned item = (unsigned)lo * (unsigned)tg.nt + (r - img_base[lo]);
+        if (threadIdx.x == 0) r_next = atomicAdd(&ctl->next, 1u);   // consumed after the bin
+        const unsigned e = worklist[r];                               // image * nt + bin
         RAC_PHASE(0);
-        raster_tile(smem_raw, s_ctl, s_scan, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_tri,
-                    recs, desc, refs, rgba_out, depth_out, lo, (int)worklist[item] RAC_PHASE_PASS);
+        raster_tile(sm, s_ctl, s_scan, &s_sc, my_scratch, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_cnt,
+                    large_tri, recs, desc, refs, rgba_out, depth_out, (int)(e / (unsigned)tg.nt), (int)(e % (unsigned)tg.nt) RAC_PHASE_PASS);
         RAC_PHASE(11);
-        __syncthreads();                  // every thread has read s_item (and left the tile's shared memory)
+        __syncthreads();                  // every thread has read s_item (and left the bin's shared memory)
         if (threadIdx.x == 0) s_item = r_next;
         __syncthreads();
         RAC_PHASE(12);

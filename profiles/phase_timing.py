@@ -12,7 +12,6 @@ sys.path[:0] = [PKG, ROOT]
 NAMES = ["item decode", "descriptors+scan+gather", "coverage (flat)", "  barrier after flat", "medium tris", "large list",
          "R1 sample analysis", "  barrier", "R2 shading", "  barrier", "R3 resolve+store", "reduce+atomics", "  next-item hand-over"]
 
-
 def main():
     import importlib.util
     spec = importlib.util.spec_from_file_location("_rac_build", os.path.join(PKG, "build.py"))
@@ -37,7 +36,7 @@ def main():
     for it in range(6):
         rac.render_concat_device(sets[it % len(sets)]["T_init"], mesh, K, (W, H), gt)
         torch.cuda.synchronize()
-        ws = list(R._ws_cache.values())[0]
+        ws = max(R._ws_cache.values(), key=lambda w: w.numel())
         base = (ws.data_ptr() + 255) // 256 * 256 - ws.data_ptr()
         off = base + (64 * B + 255) // 256 * 256            # WorkCtl follows the ImgStats block
         ctl = ws[off:off + 256].cpu().numpy().view(np.uint32)
