@@ -296,7 +296,8 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
     RAC_PHASE(7);
     const int nitems = *q_count;
     if (nitems > 0) {       // CTA-uniform
-        const ShadeCtx sc = *s_sc;      // built once per bin by thread 0, long before this point
+        const ShadeCtx& sc = *s_sc;     // built once per bin by the last thread, long before this point; read in place
+                                        // (shared memory): keeps ~28 values out of the registers of the shading loop
         for (int it = tid; it < nitems; it += kRasterThreads) {
             const int code = sitems[it];
             const int p = code & 1023, s = code >> 10;
