@@ -51,7 +51,7 @@ struct __align__(16) RasterSmem {
     int queue[kQueueCap];                          //  4 KB gathered triangle ids
     int medq[kRasterThreads];                      //  1 KB batch-local ids of medium triangles
     int tri[kRasterThreads * kTriStride];          // 20 KB staged triangles of the current batch
-    unsigned short items[kRasterWarpsN * 32 * kSmallPix];   // 8 KB per-warp flattened (triangle, pixel) items; resolve: (pixel, sample) items
+    unsigned short items[kRasterThreads * kSmallPix];       // 8 KB flattened (triangle, pixel) items of the batch; resolve: (pixel, sample) items
     unsigned slots[kBatch + 1];                    //  1 KB local id - 1 -> triangle id
 };
 constexpr size_t kRasterSmemBytes = sizeof(RasterSmem);
@@ -133,12 +133,11 @@ struct BinCtx {
 // triangle and a 16-pixel triangle in the same warp cost 17 items, not 2 x 16.  Triangles with more than kSmallPix
 // bbox pixels (and every LARGE one: int64 edge functions) take the warp-per-triangle path.  Called by all threads.
 template <bool LARGE>
-__device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, const BinCtx& bc, const int* ids, int n,
-                                              unsigned first_local RAC_PHASE_ARGS) {
+__device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, unsigned* s_wsum, const BinCtx& bc, const int* ids,
+                                              int n, unsigned first_local RAC_PHASE_ARGS) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int SX[4] = {96, 224, 32, 160};
     constexpr int SY[4] = {32, 96, 160, 224};
-    unsigned short* items = sm.items + warp * (32 * kSmallPix);
     int nit = 0, w = 0, h = 0;
     if (tid < n) {
         const unsigned tri = (unsigned)ids[tid];
@@ -175,24 +174,35 @@ __device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, co
         }
     }
     if (!LARGE) {
+        // CTA-wide item list: the (triangle, pixel) items of the whole batch are concatenated and walked 256 per step,
+        // so no warp waits at the barrier below for a neighbour that happened to draw the 16-pixel triangles
         int incl = nit;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int v = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += v;
         }
-        const int total = __shfl_sync(0xffffffffu, incl, 31);
-        if (nit) {
-            int idx = incl - nit;
-            for (int dy = 0; dy < h; ++dy)
-                for (int dx = 0; dx < w; ++dx) items[idx++] = (unsigned short)(lane | (dx << 5) | (dy << 9));
+        if (lane == 31) s_wsum[warp] = (unsigned)incl;
+        __syncthreads();
+        int wbase = 0, total = 0;
+#pragma unroll
+        for (int w2 = 0; w2 < kRasterWarpsN; ++w2) {
+            const int v = (int)s_wsum[w2];
+            if (w2 < warp) wbase += v;
+            total += v;
         }
-        __syncwarp();
+        if (nit) {
+            int idx = wbase + incl - nit;
+            for (int dy = 0; dy < h; ++dy)
+                for (int dx = 0; dx < w; ++dx) sm.items[idx++] = (unsigned short)(tid | (dx << 8) | (dy << 12));
+        }
+        __syncthreads();
+        RAC_PHASE(13);
         const float c0 = bc.c0, c1 = bc.c1;
-        for (int j = lane; j < total; j += 32) {
-            const int code = items[j];
-            const int dxp = (code >> 5) & 15, dyp = code >> 9;
-            const int4* slot = reinterpret_cast<const int4*>(sm.tri + ((warp << 5) + (code & 31)) * kTriStride);
+        for (int j = tid; j < total; j += kRasterThreads) {
+            const int code = sm.items[j];
+            const int dxp = (code >> 8) & 15, dyp = code >> 12;
+            const int4* slot = reinterpret_cast<const int4*>(sm.tri + (code & 255) * kTriStride);
             const int4 a = slot[0], b = slot[1], c = slot[2], d = slot[3];
             const int sx = dxp * kSubpix, sy = dyp * kSubpix;
             const float gx = __int_as_float(c.w), gy = __int_as_float(d.x), iz0 = __int_as_float(d.y);
@@ -418,7 +428,7 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
                 commit_bin(sm, q_count, bc, scratch_col, s_sc, S RAC_PHASE_PASS);
                 nslots = 0;
             }
-            process_batch<LARGE>(sm, med_count, bc, sm.queue + qb, n, (unsigned)nslots + 1u RAC_PHASE_PASS);
+            process_batch<LARGE>(sm, med_count, s_wsum, bc, sm.queue + qb, n, (unsigned)nslots + 1u RAC_PHASE_PASS);
             nslots += n;
         }
     };
