@@ -58,7 +58,7 @@ struct TileGrid {
 // Device-side work-list control: setup appends non-empty bins, the persistent raster warps pop their quarters.
 struct WorkCtl {
     unsigned n_work;     // bins appended by setup_kernel over all images
-    unsigned next;       // next raster item (4 per bin)
+    unsigned next;       // next raster item
     unsigned pad[62];    // (diagnostic builds accumulate phase cycle counts here)
 };
 static_assert(sizeof(WorkCtl) == 256, "WorkCtl must be 256 B");

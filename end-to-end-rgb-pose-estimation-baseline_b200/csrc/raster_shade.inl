@@ -69,7 +69,8 @@ __device__ __forceinline__ void persp_bary(const TriGeom& g, int Px, int Py, flo
 
 // COLOR_0 / texture modulation of the base colour (R7 "x COLOR_0", R8) at subpixel point (Pcx, Pcy).  Kept out of line:
 // the raster warps of an SM run at unrelated program counters, so the kernel's hot instruction footprint matters.
-__device__ __noinline__ void shade_base_color(const ShadeCtx& sc, const TriGeom& g, unsigned tri, int Pcx, int Pcy, float* base) {
+__device__ __noinline__ void shade_base_color(const ShadeCtx& sc, const int4* __restrict__ rec, unsigned tri, int Pcx, int Pcy, float* base) {
+        const TriGeom g = unpack_geom(rec[0], rec[1], rec[2]);
         float w0, w1, w2;
         persp_bary(g, Pcx, Pcy, w0, w1, w2);
         // record order is (v0, v2, v1) of the mesh face (setup swaps v1 <-> v2)
@@ -114,13 +115,21 @@ __device__ __noinline__ void shade_base_color(const ShadeCtx& sc, const TriGeom&
         }
 }
 
+// What the shading of one triangle needs beyond the context: its 1/z plane (relative to vertex 0) and its camera-frame
+// normal.  raster_kernel keeps one per batch-local id in shared memory (the staged slot), so the untextured path never
+// goes back to the 48-B record in global memory.
+struct ShadeTri {
+    int X0, Y0;            // vertex 0 in subpixels
+    float gx, gy, iz0;
+    float nx, ny, nz;
+};
+
 // RS-S: shade triangle `tri` at the centre of pixel (px,py); returns RGBA8 packed little-endian.
-__device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __restrict__ rec, unsigned tri, int px, int py) {
-    const int4 q0 = rec[0], q1 = rec[1], q2 = rec[2];
-    const TriGeom g = unpack_geom(q0, q1, q2);
-    const float nx = __int_as_float(q2.y), ny = __int_as_float(q2.z), nz = __int_as_float(q2.w);
+// `rec` (the record in global memory) is only read for vertex-coloured / textured meshes.
+__device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const ShadeTri& t, const int4* __restrict__ rec, unsigned tri, int px, int py) {
+    const float nx = t.nx, ny = t.ny, nz = t.nz;
     const int Pcx = px * kSubpix + 128, Pcy = py * kSubpix + 128;
-    float iz = fmaf(g.gy, (float)(Pcy - g.Y0), fmaf(g.gx, (float)(Pcx - g.X0), g.iz0));
+    float iz = fmaf(t.gy, (float)(Pcy - t.Y0), fmaf(t.gx, (float)(Pcx - t.X0), t.iz0));
     iz = fminf(fmaxf(iz, sc.iz_min), sc.iz_max);
     const float z = __fdividef(1.0f, iz);   // fast-math shading: colour parity bar is 2/255 (north_star), not bit-exactness
     const float x = ((px + 0.5f) - sc.cx) * sc.fx_inv * z;
@@ -139,7 +148,7 @@ __device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const int4* __rest
     const float radiance = att * sc.intensity;
 
     float base[3] = {sc.base[0], sc.base[1], sc.base[2]};
-    if (sc.vcolor || sc.tex) shade_base_color(sc, g, tri, Pcx, Pcy, base);   // out of line: cold for untextured meshes
+    if (sc.vcolor || sc.tex) shade_base_color(sc, rec, tri, Pcx, Pcy, base);   // out of line: cold for untextured meshes
 
     // metallic-roughness BRDF with v = l = h: vh = 1 -> Fresnel = f0
     const float kk = sc.kgeo;

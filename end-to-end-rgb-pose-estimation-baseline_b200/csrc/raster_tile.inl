@@ -50,9 +50,10 @@ struct __align__(16) RasterSmem {
     unsigned z[4 * kTilePix];                      //  8 KB keys, sample-major: z[s * 512 + p]
     int queue[kQueueCap];                          //  4 KB gathered triangle ids
     int medq[kRasterThreads];                      //  1 KB batch-local ids of medium triangles
-    int tri[kRasterThreads * kTriStride];          // 20 KB staged triangles of the current batch
+    int tri[kRasterThreads * kTriStride];          // 20 KB staged triangles by local id - 1: edge equations (coverage) + plane, normal (shading)
     unsigned short items[kRasterThreads * kSmallPix];       // 8 KB flattened (triangle, pixel) items of the batch; resolve: (pixel, sample) items
-    unsigned slots[kBatch + 1];                    //  1 KB local id - 1 -> triangle id
+    unsigned slots[kBatch + 2];                    //  1 KB local id - 1 -> triangle id
+    unsigned cols[4 * kTilePix];                   //  8 KB resolve: colour of each pixel's representative samples
 };
 constexpr size_t kRasterSmemBytes = sizeof(RasterSmem);
 
@@ -139,6 +140,7 @@ __device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, un
     constexpr int SX[4] = {96, 224, 32, 160};
     constexpr int SY[4] = {32, 96, 160, 224};
     int nit = 0, w = 0, h = 0;
+    const int slot_id = (int)first_local - 1 + tid;       // = local id - 1 (< 254)
     if (tid < n) {
         const unsigned tri = (unsigned)ids[tid];
         const unsigned local = first_local + (unsigned)tid;
@@ -150,6 +152,11 @@ __device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, un
         tri_bbox(g, bc.x_lo, bc.x_hi, bc.y_lo, bc.y_hi, bx0, bx1, by0, by1);
         if (bx0 <= bx1 && by0 <= by1) {
             w = bx1 - bx0 + 1; h = by1 - by0 + 1;
+            // the slot of this local id: shading data always (it lives until the next commit / the final resolve),
+            // edge equations relative to the clipped bbox origin for the flattened coverage pass
+            int4* slot = reinterpret_cast<int4*>(sm.tri + (local - 1u) * kTriStride);
+            slot[3] = make_int4(__float_as_int(g.gy), __float_as_int(g.iz0), g.X0, g.Y0);
+            slot[4] = make_int4(q2.y, q2.z, q2.w, __float_as_int(g.gx));
             if (!LARGE && w * h <= kSmallPix) {
                 nit = w * h;
                 const int dx0 = g.X1 - g.X0, dy0 = g.Y1 - g.Y0;
@@ -159,15 +166,12 @@ __device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, un
                 const int b1 = (dy1 < 0 || (dy1 == 0 && dx1 > 0)) ? 0 : -1;
                 const int b2 = (dy2 < 0 || (dy2 == 0 && dx2 > 0)) ? 0 : -1;
                 const int ox = bx0 * kSubpix, oy = by0 * kSubpix;
-                int4* slot = reinterpret_cast<int4*>(sm.tri + tid * kTriStride);
                 const int C0 = dx0 * (oy - g.Y0) - dy0 * (ox - g.X0) + b0;
                 const int C1 = dx1 * (oy - g.Y1) - dy1 * (ox - g.X1) + b1;
                 const int C2 = dx2 * (oy - g.Y2) - dy2 * (ox - g.X2) + b2;
                 slot[0] = make_int4(-dy0, dx0, C0, -dy1);
                 slot[1] = make_int4(dx1, C1, -dy2, dx2);
-                slot[2] = make_int4(C2, ox - g.X0, oy - g.Y0, __float_as_int(g.gx));
-                slot[3] = make_int4(__float_as_int(g.gy), __float_as_int(g.iz0), (int)local,
-                                    (by0 - bc.y_lo) * kTileW + (bx0 - bc.x_lo));
+                slot[2] = make_int4(C2, ox, oy, (by0 - bc.y_lo) * kTileW + (bx0 - bc.x_lo));
             } else {
                 sm.medq[atomicAdd(med_count, 1)] = tid;
             }
@@ -194,7 +198,7 @@ __device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, un
         if (nit) {
             int idx = wbase + incl - nit;
             for (int dy = 0; dy < h; ++dy)
-                for (int dx = 0; dx < w; ++dx) sm.items[idx++] = (unsigned short)(tid | (dx << 8) | (dy << 12));
+                for (int dx = 0; dx < w; ++dx) sm.items[idx++] = (unsigned short)(slot_id | (dx << 8) | (dy << 12));
         }
         __syncthreads();
         RAC_PHASE(13);
@@ -205,8 +209,10 @@ __device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, un
             const int4* slot = reinterpret_cast<const int4*>(sm.tri + (code & 255) * kTriStride);
             const int4 a = slot[0], b = slot[1], c = slot[2], d = slot[3];
             const int sx = dxp * kSubpix, sy = dyp * kSubpix;
-            const float gx = __int_as_float(c.w), gy = __int_as_float(d.x), iz0 = __int_as_float(d.y);
-            const int pidx = d.w + dyp * kTileW + dxp;
+            const float gx = __int_as_float(slot[4].w), gy = __int_as_float(d.x), iz0 = __int_as_float(d.y);
+            const int rx = c.y - d.z, ry = c.z - d.w;       // bbox origin relative to vertex 0
+            const int pidx = c.w + dyp * kTileW + dxp;
+            const unsigned local = (unsigned)(code & 255) + 1u;
 #pragma unroll
             for (int s = 0; s < 4; ++s) {
                 const int ux = sx + SX[s], uy = sy + SY[s];
@@ -214,9 +220,9 @@ __device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, un
                 const int e1 = b.y + a.w * ux + b.x * uy;
                 const int e2 = c.x + b.z * ux + b.w * uy;
                 if ((e0 | e1 | e2) >= 0) {
-                    const float fxr = (float)(c.y + ux), fyr = (float)(c.z + uy);
+                    const float fxr = (float)(rx + ux), fyr = (float)(ry + uy);
                     const float iz = __fmaf_rn(gy, fyr, __fmaf_rn(gx, fxr, iz0));
-                    const unsigned key = depth_key(iz, c0, c1, (unsigned)d.z);
+                    const unsigned key = depth_key(iz, c0, c1, local);
                     if (key != kKeyEmpty32) atomicMin(&sm.z[s * kTilePix + pidx], key);
                 }
             }
@@ -265,7 +271,7 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
     const int tid = threadIdx.x, lane = tid & 31;
     const int tw = bc.x_hi - bc.x_lo + 1, th = bc.y_hi - bc.y_lo + 1;
     unsigned short* sitems = sm.items;   // [4 * kTilePix] of the 4096: free between batches (the queue is NOT: a commit runs mid-queue)
-    unsigned* cols = reinterpret_cast<unsigned*>(sm.tri);   // [4 * kTilePix] colour of each representative sample (staging area is idle here)
+    unsigned* cols = sm.cols;            // [4 * kTilePix] colour of each representative sample
     constexpr int kPer = kTilePix / kRasterThreads;
     // R1.  Nothing is kept in registers across the shading pass: R3 re-derives the representatives from the keys.
 #pragma unroll
@@ -312,8 +318,14 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
             const int code = sitems[it];
             const int p = code & 1023, s = code >> 10;
             const unsigned key = sm.z[s * kTilePix + p];
-            const unsigned tri = sm.slots[(key & 0xFFu) - 1u];
-            const unsigned col = shade(sc, bc.img_recs + 3 * (size_t)tri, tri, bc.x_lo + (p & (kTileW - 1)), bc.y_lo + p / kTileW);
+            const unsigned id1 = (key & 0xFFu) - 1u;
+            const unsigned tri = sm.slots[id1];
+            const int4* slot = reinterpret_cast<const int4*>(sm.tri + id1 * kTriStride);
+            const int4 d = slot[3], e = slot[4];
+            ShadeTri st;
+            st.X0 = d.z; st.Y0 = d.w; st.gy = __int_as_float(d.x); st.iz0 = __int_as_float(d.y);
+            st.nx = __int_as_float(e.x); st.ny = __int_as_float(e.y); st.nz = __int_as_float(e.z); st.gx = __int_as_float(e.w);
+            const unsigned col = shade(sc, st, bc.img_recs + 3 * (size_t)tri, tri, bc.x_lo + (p & (kTileW - 1)), bc.y_lo + p / kTileW);
             if (FINAL) {
                 cols[s * kTilePix + p] = col;      // R3 finds it through the representative index
             } else {
@@ -573,6 +585,13 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
     long long g_phase_t = clock64();
 #endif
     RAC_TL(2);
+#ifdef RAC_PHASE_TIMING
+    if (threadIdx.x == 0) {      // sum of CTA start times (ns since the epoch in g_tl[15], set by the host to ~now)
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicAdd(&g_tl[9], t - g_tl[15]);
+    }
+#endif
     if (threadIdx.x == 0) { s_item = atomicAdd(&ctl->next, 1u); s_ctl[0] = 0; s_ctl[1] = 0; }
     __syncthreads();
     for (;;) {
@@ -590,5 +609,12 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
         __syncthreads();
         RAC_PHASE(12);
     }
+#ifdef RAC_PHASE_TIMING
+    if (threadIdx.x == 0) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        atomicAdd(&g_tl[10], t - g_tl[15]);
+    }
+#endif
     RAC_TL(2);
 }

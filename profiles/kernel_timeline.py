@@ -42,6 +42,7 @@ def main():
     buf = (ctypes.c_ulonglong * 16)()
     acc = np.zeros((4, 2))
     n = 0
+    cta_start, cta_end = [], []
     from rac import render as R
     cyc = 0.0
     for it in range(12):
@@ -51,6 +52,11 @@ def main():
         torch.cuda.synchronize()
         dbg(buf, 0)
         late = buf[8]
+        if it >= 4:
+            g = buf[4 * 1 + 0]      # raster first start (index 2*2)
+            ncta = 592
+            ep = buf[15]
+            cta_start.append(buf[9] / ncta - (buf[4] - ep)); cta_end.append((buf[5] - ep) - buf[10] / ncta)
         t = np.array(list(buf), dtype=np.float64).reshape(8, 2)[:4]
         valid = t[:, 1] > 0
         t0 = t[valid, 0].min()
@@ -62,6 +68,8 @@ def main():
             off = base + (64 * B + 255) // 256 * 256            # WorkCtl follows the ImgStats block
             ctl = ws[off:off + 256].cpu().numpy().view(np.uint32)
             cyc += float(ctl[2:64].copy().view(np.uint64)[:13].sum())
+    print("raster: mean CTA start lag %.1f us after the first CTA, mean CTA finish %.1f us before the last (592 CTAs assumed)"
+          % (np.mean(cta_start) / 1e3, np.mean(cta_end) / 1e3))
     print("raster CTAs that started > 10 us after the first (last replay): %d" % late)
     print("raster CTA cycles (sum over CTAs, thread 0 clock64): %.1f M per call" % (cyc / n / 1e6))
     for nm, (a, b) in zip(NAMES, acc / n):
