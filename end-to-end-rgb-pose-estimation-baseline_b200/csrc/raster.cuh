@@ -60,8 +60,10 @@ struct WorkCtl {
     unsigned n_work;     // bins appended by setup_kernel over all images
     unsigned next;       // next raster item
     unsigned pad[62];    // (diagnostic builds accumulate phase cycle counts here)
+    unsigned ordered;    // 1 = raster reads worklist_sorted (order_kernel)
+    unsigned pad2[63];
 };
-static_assert(sizeof(WorkCtl) == 256, "WorkCtl must be 256 B");
+static_assert(sizeof(WorkCtl) == 512, "WorkCtl must be 512 B");
 
 struct RenderWs {
     ImgStats* stats;
@@ -73,11 +75,13 @@ struct RenderWs {
     unsigned char* refs;   // [B][ncta_max][1024] local triangle ids grouped by bin
     WorkCtl* ctl;          // work-list counters (zeroed with stats and flags by one memset)
     unsigned* flags;       // [B][nt] 1 = bin is on the work list
+    unsigned* loads;       // [B][nt] load estimate of the bin
     unsigned* worklist;    // [B * nt] non-empty bins (image * nt + bin), appended by setup
+    unsigned* worklist_sorted;  // [min(B * nt, kOrderMax)] the same, heaviest first (order_kernel)
     unsigned* scratch_col; // [raster CTAs][4][512] committed colours of bins with more than 254 triangles
     unsigned* rgba;        // [B][H][W] resolved RGBA8 (non-empty bins only)
     float* depth;          // [B][H][W] metric depth (non-empty bins only)
-    size_t zero_bytes;     // bytes from `stats` that every call zeroes (stats + ctl + flags)
+    size_t zero_bytes;     // bytes from `stats` that every call zeroes (stats + ctl + flags + loads)
     size_t total;
 };
 

@@ -39,11 +39,14 @@ __device__ __forceinline__ bool project_vertex(const CamPose& c, const float* __
 }
 
 // The first triangle to touch a bin appends (image, bin) to the flat raster work list: one exchange per bin, everyone
-// else sees the 1 with a plain load.  (Ordering the list by load — heaviest bins first, built by the last setup CTA
-// behind a ticket — was measured: it shortens raster_kernel's tail by ~2 us and lengthens this kernel by ~12.)
-__device__ __forceinline__ void mark_tile(WorkCtl* ctl, unsigned* flags, unsigned* worklist, unsigned b, unsigned nt, unsigned tile) {
+// else sees the 1 with a plain load.  Every toucher also adds to the bin's load estimate (binned triangle refs +
+// kLargeWeight per large triangle) with a fire-and-forget reduction; order_kernel sorts the list by it.
+constexpr unsigned kLargeWeight = 16u;
+__device__ __forceinline__ void mark_tile(WorkCtl* ctl, unsigned* flags, unsigned* loads, unsigned* worklist, unsigned b, unsigned nt,
+                                          unsigned tile, unsigned weight) {
     const size_t i = (size_t)b * nt + tile;
     if (flags[i] == 0u && atomicExch(flags + i, 1u) == 0u) worklist[atomicAdd(&ctl->n_work, 1u)] = b * nt + tile;
+    atomicAdd(loads + i, weight);
 }
 
 // One CTA = kSetupThreads consecutive triangles of one image.  Survivors that touch at most 2x2 tiles are
@@ -58,7 +61,7 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
              float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_cnt, unsigned* __restrict__ large_tri,
              int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs,
-             WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ worklist) {
+             WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ loads, unsigned* __restrict__ worklist) {
     __shared__ unsigned s_cnt[kMaxBinTiles];
     __shared__ unsigned s_off[kMaxBinTiles];
     __shared__ unsigned s_warp[kSetupThreads / 32];
@@ -145,7 +148,7 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         if (large) {
             large_tri[(size_t)b * maxT + (size_t)blockIdx.x * kSetupThreads + base + __popc(m & ((1u << lane) - 1u))] = (unsigned)t;
             for (int ty = ty0; ty <= ty1; ++ty)
-                for (int tx = tx0; tx <= tx1; ++tx) mark_tile(ctl, flags, worklist, (unsigned)b, (unsigned)tg.nt, (unsigned)(ty * tg.ntx + tx));
+                for (int tx = tx0; tx <= tx1; ++tx) mark_tile(ctl, flags, loads, worklist, (unsigned)b, (unsigned)tg.nt, (unsigned)(ty * tg.ntx + tx), kLargeWeight);
         }
     }
     if (!tg.binned) return;   // CTA-uniform
@@ -170,7 +173,7 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         const unsigned c = s_cnt[i];
         s_off[i] = run;
         dimg[(size_t)i * tg.ncta_max] = (run << 16) | c;    // offset <= 1024, count <= 256
-        if (c) mark_tile(ctl, flags, worklist, (unsigned)b, (unsigned)tg.nt, (unsigned)i);
+        if (c) mark_tile(ctl, flags, loads, worklist, (unsigned)b, (unsigned)tg.nt, (unsigned)i, c);
         run += c;
     }
     __syncthreads();
@@ -187,9 +190,59 @@ setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids
              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
              float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_cnt, unsigned* __restrict__ large_tri,
              int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs,
-             WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ worklist) {
+             WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ loads, unsigned* __restrict__ worklist) {
     RAC_TL(1);
     setup_body(table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, znear, stats, large_cnt, large_tri, recs, desc, refs, ctl,
-               flags, worklist);
+               flags, loads, worklist);
     RAC_TL(1);
+}
+
+// One CTA orders the work list by decreasing load estimate (counting sort into 128 buckets): the persistent raster
+// CTAs then start with the heaviest bins and finish with the lightest, which keeps the tail of raster_kernel short
+// when there are only a few bins per CTA (2 400 bins over 592 CTAs at the bench workload: the mean CTA used to sit
+// idle for the last quarter of the kernel).  Lists longer than kOrderMax are left as they are: with that many items
+// per CTA the order does not matter.
+constexpr unsigned kOrderMax = 16384;
+constexpr int kOrderThreads = 1024;
+__global__ void __launch_bounds__(kOrderThreads)
+order_kernel(WorkCtl* __restrict__ ctl, const unsigned* __restrict__ loads, const unsigned* __restrict__ worklist,
+             unsigned* __restrict__ worklist_sorted) {
+    __shared__ unsigned s_hist[128];
+    const unsigned n = ctl->n_work;
+    if (n > kOrderMax) return;
+    const int tid = threadIdx.x;
+    if (tid < 128) s_hist[tid] = 0u;
+    __syncthreads();
+    unsigned e[kOrderMax / kOrderThreads], bk[kOrderMax / kOrderThreads];
+#pragma unroll
+    for (int k = 0; k < (int)(kOrderMax / kOrderThreads); ++k) {
+        const unsigned i = (unsigned)tid + (unsigned)k * kOrderThreads;
+        if (i < n) {
+            e[k] = worklist[i];
+            bk[k] = 127u - min(loads[e[k]] >> 3, 127u);                   // bucket 0 = heaviest
+            atomicAdd(&s_hist[bk[k]], 1u);
+        }
+    }
+    __syncthreads();
+    if (tid < 32) {        // exclusive scan of the 128 bucket sizes -> bucket cursors
+        unsigned v[4], sum = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { v[k] = s_hist[4 * tid + k]; sum += v[k]; }
+        unsigned incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned u = __shfl_up_sync(0xffffffffu, incl, o);
+            if (tid >= o) incl += u;
+        }
+        unsigned run = incl - sum;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { s_hist[4 * tid + k] = run; run += v[k]; }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < (int)(kOrderMax / kOrderThreads); ++k) {
+        const unsigned i = (unsigned)tid + (unsigned)k * kOrderThreads;
+        if (i < n) worklist_sorted[atomicAdd(&s_hist[bk[k]], 1u)] = e[k];
+    }
+    if (tid == 0) ctl->ordered = 1u;
 }

@@ -570,8 +570,8 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
               const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
               SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_cnt,
               const unsigned* __restrict__ large_tri, const int4* __restrict__ recs, const unsigned* __restrict__ desc,
-              const unsigned char* __restrict__ refs, WorkCtl* __restrict__ ctl, const unsigned* __restrict__ worklist,
-              unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, unsigned* __restrict__ scratch_col) {
+              const unsigned char* __restrict__ refs, WorkCtl* __restrict__ ctl, const unsigned* __restrict__ worklist_any,
+              const unsigned* __restrict__ worklist_sorted, unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, unsigned* __restrict__ scratch_col) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RasterSmem& sm = *reinterpret_cast<RasterSmem*>(smem_raw);
     __shared__ int s_ctl[2];
@@ -579,6 +579,7 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
     __shared__ unsigned s_scan[3 * kRasterThreads + kRasterWarpsN];
     __shared__ ShadeCtx s_sc;
     const unsigned n_work = __ldcg(&ctl->n_work);    // final: written by setup_kernel (previous launch)
+    const unsigned* worklist = __ldcg(&ctl->ordered) ? worklist_sorted : worklist_any;
     unsigned* my_scratch = scratch_col + (size_t)blockIdx.x * kScratchPerCta;
 #ifdef RAC_PHASE_TIMING
     WorkCtl* g_phase_ctl = ctl;
