@@ -79,13 +79,18 @@ finalize_live_kernel(FinArgs A, TileGrid tg, int H, const unsigned* __restrict__
     const int W = A.W, npix = A.npix;
     const int C = A.use_norm_depth ? 7 : 6;
     const int ly = threadIdx.x >> 3, lx = (threadIdx.x & 7) << 2;
+    __shared__ float s_lut[256];      // q / qmax for the 256 possible 8-bit values of this image (R9): 256 divisions per
+                                      // bin instead of 1536
     for (unsigned r = blockIdx.x; r < n_work; r += gridDim.x) {
         const unsigned e = worklist[r];
         const int b = (int)(e / (unsigned)tg.nt), tile = (int)(e % (unsigned)tg.nt);
         const int x = (tile % tg.ntx) * kTileW + lx, y = (tile / tg.ntx) * kTileH + ly;
-        if (y >= H || x >= W) continue;
         const ImgStats st = load_stats_cg(A.stats + b);
         const NormConsts n = load_norm(st, A.use_norm_depth != 0);
+        __syncthreads();              // previous bin's lookups are done
+        for (int q = threadIdx.x; q < 256; q += kFinThreads) s_lut[q] = norm_col1((unsigned)q, n);
+        __syncthreads();
+        if (y >= H || x >= W) continue;
         const size_t pi = (size_t)b * npix + (size_t)y * W + x;
         const int nv = min(4, W - x);
         unsigned c[4] = {0u, 0u, 0u, 0u};
@@ -104,7 +109,7 @@ finalize_live_kernel(FinArgs A, TileGrid tg, int H, const unsigned* __restrict__
         float rr[4], gg[4], bb[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            rr[i] = norm_col1(c[i] & 0xFFu, n); gg[i] = norm_col1((c[i] >> 8) & 0xFFu, n); bb[i] = norm_col1((c[i] >> 16) & 0xFFu, n);
+            rr[i] = s_lut[c[i] & 0xFFu]; gg[i] = s_lut[(c[i] >> 8) & 0xFFu]; bb[i] = s_lut[(c[i] >> 16) & 0xFFu];
         }
         if (A.vec) {
             if (A.x_nchw) {

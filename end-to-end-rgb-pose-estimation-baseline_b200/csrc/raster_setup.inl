@@ -29,7 +29,7 @@ __device__ __forceinline__ bool project_vertex(const CamPose& c, const float* __
     const float yc = __fmaf_rn(c.r[5], pz, __fmaf_rn(c.r[4], py, __fmaf_rn(c.r[3], px, c.t[1])));
     const float zc = __fmaf_rn(c.r[8], pz, __fmaf_rn(c.r[7], py, __fmaf_rn(c.r[6], px, c.t[2])));
     if (!(zc >= znear)) return false;
-    iz = __fdiv_rn(1.0f, zc);
+    iz = __frcp_rn(zc);      // correctly rounded: == 1.0f / zc
     const float u = __fmaf_rn(c.fx, __fmul_rn(xc, iz), c.cx);
     const float v = __fmaf_rn(c.fy, __fmul_rn(yc, iz), c.cy);
     if (!(fabsf(u) <= kGuardPx) || !(fabsf(v) <= kGuardPx)) return false;
@@ -63,6 +63,8 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
              int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs,
              WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ loads, unsigned* __restrict__ worklist) {
     __shared__ unsigned s_cnt[kMaxBinTiles];
+    __shared__ __align__(16) unsigned char s_refs[4 * kSetupThreads];
+    __shared__ unsigned s_total;
     __shared__ unsigned s_off[kMaxBinTiles];
     __shared__ unsigned s_warp[kSetupThreads / 32];
     const int b = blockIdx.y;
@@ -176,12 +178,19 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         if (c) mark_tile(ctl, flags, loads, worklist, (unsigned)b, (unsigned)tg.nt, (unsigned)i, c);
         run += c;
     }
+    if (tid == kSetupThreads - 1) s_total = run;          // this thread owns the last bins: run = all refs of the CTA
     __syncthreads();
+    // refs: grouped by bin in shared memory first, then copied out with 16-B stores (not ~350 scattered 1-B ones)
     if (small) {
-        unsigned char* region = refs + (((size_t)b * tg.ncta_max + blockIdx.x) << 10);
         int k = 0;
         for (int ty = ty0; ty <= ty1; ++ty)
-            for (int tx = tx0; tx <= tx1; ++tx) region[s_off[ty * tg.ntx + tx] + slot[k++]] = (unsigned char)tid;
+            for (int tx = tx0; tx <= tx1; ++tx) s_refs[s_off[ty * tg.ntx + tx] + slot[k++]] = (unsigned char)tid;
+    }
+    __syncthreads();
+    {
+        uint4* region = reinterpret_cast<uint4*>(refs + (((size_t)b * tg.ncta_max + blockIdx.x) << 10));
+        const int n16 = ((int)s_total + 15) >> 4;
+        if (tid < n16) region[tid] = reinterpret_cast<const uint4*>(s_refs)[tid];     // <= 64 stores of 16 B
     }
 }
 
