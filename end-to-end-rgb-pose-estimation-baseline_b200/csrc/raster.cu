@@ -87,14 +87,12 @@ static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
     const TileGrid tg = make_tile_grid(W, H, maxT);
     const size_t ndesc = tg.binned ? (size_t)B * tg.nt * tg.ncta_max : 0;
     const size_t nrefs = tg.binned ? ((size_t)B * tg.ncta_max) << 10 : 0;
-    // [stats | ctl | flags] form one contiguous block that a single memset zeroes per call
+    // [stats | ctl | loads] form one contiguous block that a single memset zeroes per call
     w.stats = (ImgStats*)(p + off);          off = align256(off + sizeof(ImgStats) * (size_t)B);
     w.ctl = (WorkCtl*)(p + off);             off = align256(off + sizeof(WorkCtl));
-    w.flags = (unsigned*)(p + off);          off = align256(off + sizeof(unsigned) * (size_t)B * tg.nt);
     w.loads = (unsigned*)(p + off);          off = align256(off + sizeof(unsigned) * (size_t)B * tg.nt);
     w.zero_bytes = off;
-    w.worklist = (unsigned*)(p + off);       off = align256(off + sizeof(unsigned) * (size_t)B * tg.nt);
-    w.worklist_sorted = (unsigned*)(p + off); off = align256(off + sizeof(unsigned) * min((size_t)B * tg.nt, (size_t)kOrderMax));
+    w.buckets = (unsigned*)(p + off);        off = align256(off + sizeof(unsigned) * (size_t)kBuckets * B * tg.nt);
     w.mesh_ids = (int*)(p + off);            off = align256(off + sizeof(int) * (size_t)B);
     w.large_cnt = (unsigned*)(p + off);      off = align256(off + sizeof(unsigned) * (size_t)B * tg.ncta_max);
     w.large_tri = (unsigned*)(p + off);      off = align256(off + sizeof(unsigned) * (size_t)B * maxT);
@@ -267,7 +265,6 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         // every kernel of the call uses raster_kernel's L1 / shared-memory split, so that CTAs of the forked kernel and
         // of the main chain can share an SM (an SM does not mix carve-outs)
         RAC_CUDA_CHECK(cudaFuncSetAttribute(setup_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        RAC_CUDA_CHECK(cudaFuncSetAttribute(order_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         RAC_CUDA_CHECK(cudaFuncSetAttribute(finalize_live_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         carve_configured = true;
     }
@@ -289,12 +286,8 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         dim3 grid(tg.ncta_max, B);
         setup_kernel<<<grid, kSetupThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
                                                          ws.stats, ws.large_cnt, ws.large_tri, ws.recs, ws.desc, ws.refs,
-                                                         ws.ctl, ws.flags, ws.loads, ws.worklist);
+                                                         ws.ctl, ws.loads, ws.buckets);
         RAC_LAUNCHED();
-        if ((size_t)B * tg.nt > (size_t)n_sm * 4 && !(skip & 128)) {     // enough bins for the order to matter
-            order_kernel<<<1, kOrderThreads, 0, stream>>>(ws.ctl, ws.loads, ws.worklist, ws.worklist_sorted);
-            RAC_LAUNCHED();
-        }
     }
     // fork AFTER setup: setup_kernel is bound by its own memory traffic (records, descriptors) and triples in
     // duration next to a streaming kernel, while raster_kernel is issue-bound and does not notice one
@@ -311,7 +304,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         const int grid = (int)min((long long)grid_max, (long long)B * tg.nt);
         raster_kernel<<<grid, kRasterThreads, kRasterSmemBytes, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,
                                                                           ws.stats, ws.large_cnt, ws.large_tri, ws.recs, ws.desc, ws.refs,
-                                                                          ws.ctl, ws.worklist, ws.worklist_sorted, ws.rgba, ws.depth, ws.scratch_col);
+                                                                          ws.ctl, ws.buckets, (size_t)B * tg.nt, ws.rgba, ws.depth, ws.scratch_col);
         RAC_LAUNCHED();
     }
     if (!(skip & 16)) RAC_CUDA_CHECK(cudaStreamWaitEvent(stream, side->join, 0));
@@ -321,7 +314,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         fin.vec = (W % 4 == 0 && aligned16(ws.rgba) && aligned16(ws.depth) && aligned16(fin.x_nchw) &&
                    aligned16(fin.rgb_hwc_out) && aligned16(fin.rgba_copy) && aligned16(fin.depth_out)) ? 1 : 0;
         const int grid = (int)min((long long)n_sm * 16, (long long)B * tg.nt);
-        finalize_live_kernel<<<grid, kFinThreads, 0, stream>>>(fin, tg, H, ws.worklist, ws.ctl);
+        finalize_live_kernel<<<grid, kFinThreads, 0, stream>>>(fin, tg, H, ws.buckets, (size_t)B * tg.nt, ws.ctl);
         RAC_LAUNCHED();
     }
     return RAC_OK;

@@ -38,7 +38,9 @@ struct ImgStats {
     unsigned dcount;     // #pixels with depth > 0.01      (normalize_depth mask)
     unsigned dmax_bits;  // float bits of max depth (depth >= 0 so uint order == float order)
     double dsum, dsumsq; // over depth > 0.01
-    double pad1[4];
+    unsigned ndone;      // setup CTAs of this image that have finished (the last one publishes the image's bins)
+    unsigned pad0;
+    double pad1[3];
 };
 static_assert(sizeof(ImgStats) == 64, "ImgStats must be 64 B");
 
@@ -55,13 +57,18 @@ struct TileGrid {
     int ncta_max;        // ceil(maxT / kSetupThreads): stride of the descriptor / ref / large-list tables
 };
 
-// Device-side work-list control: setup appends non-empty bins, the persistent raster warps pop their quarters.
+// Device-side work-list control.  The non-empty bins of the batch are kept in kBuckets lists by load class
+// (bucket 0 = heaviest): the setup CTA that finishes an image last appends that image's bins to the lists, and the
+// persistent raster CTAs consume the concatenation bucket 0, 1, ... — heaviest bins first (LPT), which keeps the
+// tail of raster_kernel short when there are only a few bins per CTA, without a sorting pass between the kernels.
+constexpr int kBuckets = 16;
+constexpr int kBucketShift = 5;     // load class = min(load >> 5, 15)
 struct WorkCtl {
-    unsigned n_work;     // bins appended by setup_kernel over all images
+    unsigned pad_a;
     unsigned next;       // next raster item
     unsigned pad[62];    // (diagnostic builds accumulate phase cycle counts here)
-    unsigned ordered;    // 1 = raster reads worklist_sorted (order_kernel)
-    unsigned pad2[63];
+    unsigned bucket_cnt[kBuckets];
+    unsigned pad2[64 - kBuckets];
 };
 static_assert(sizeof(WorkCtl) == 512, "WorkCtl must be 512 B");
 
@@ -73,15 +80,13 @@ struct RenderWs {
     int4* recs;            // [B][maxT][3]
     unsigned* desc;        // [B][nt][ncta_max]  (offset << 16) | count, one per (bin, setup CTA)
     unsigned char* refs;   // [B][ncta_max][1024] local triangle ids grouped by bin
-    WorkCtl* ctl;          // work-list counters (zeroed with stats and flags by one memset)
-    unsigned* flags;       // [B][nt] 1 = bin is on the work list
-    unsigned* loads;       // [B][nt] load estimate of the bin
-    unsigned* worklist;    // [B * nt] non-empty bins (image * nt + bin), appended by setup
-    unsigned* worklist_sorted;  // [min(B * nt, kOrderMax)] the same, heaviest first (order_kernel)
+    WorkCtl* ctl;          // work-list counters (zeroed with stats and loads by one memset)
+    unsigned* loads;       // [B][nt] load estimate of the bin (0 = empty bin)
+    unsigned* buckets;     // [kBuckets][B * nt] non-empty bins (image * nt + bin) by load class
     unsigned* scratch_col; // [raster CTAs][4][512] committed colours of bins with more than 254 triangles
     unsigned* rgba;        // [B][H][W] resolved RGBA8 (non-empty bins only)
     float* depth;          // [B][H][W] metric depth (non-empty bins only)
-    size_t zero_bytes;     // bytes from `stats` that every call zeroes (stats + ctl + flags + loads)
+    size_t zero_bytes;     // bytes from `stats` that every call zeroes (stats + ctl + loads)
     size_t total;
 };
 

@@ -73,16 +73,19 @@ __device__ __forceinline__ ImgStats load_stats_cg(const ImgStats* p) {
 constexpr int kFinThreads = 128;
 
 __global__ void __launch_bounds__(kFinThreads)
-finalize_live_kernel(FinArgs A, TileGrid tg, int H, const unsigned* __restrict__ worklist, const WorkCtl* __restrict__ ctl) {
+finalize_live_kernel(FinArgs A, TileGrid tg, int H, const unsigned* __restrict__ buckets, size_t bucket_cap, const WorkCtl* __restrict__ ctl) {
     RAC_TL(3);
-    const unsigned n_work = __ldcg(&ctl->n_work);
+    __shared__ unsigned s_prefix[kBuckets + 1];
+    load_bucket_prefix(ctl, s_prefix);
+    __syncthreads();
+    const unsigned n_work = s_prefix[kBuckets];
     const int W = A.W, npix = A.npix;
     const int C = A.use_norm_depth ? 7 : 6;
     const int ly = threadIdx.x >> 3, lx = (threadIdx.x & 7) << 2;
     __shared__ float s_lut[256];      // q / qmax for the 256 possible 8-bit values of this image (R9): 256 divisions per
                                       // bin instead of 1536
     for (unsigned r = blockIdx.x; r < n_work; r += gridDim.x) {
-        const unsigned e = worklist[r];
+        const unsigned e = bucket_entry(s_prefix, buckets, bucket_cap, r);
         const int b = (int)(e / (unsigned)tg.nt), tile = (int)(e % (unsigned)tg.nt);
         const int x = (tile % tg.ntx) * kTileW + lx, y = (tile / tg.ntx) * kTileH + ly;
         const ImgStats st = load_stats_cg(A.stats + b);

@@ -38,15 +38,37 @@ __device__ __forceinline__ bool project_vertex(const CamPose& c, const float* __
     return true;
 }
 
-// The first triangle to touch a bin appends (image, bin) to the flat raster work list: one exchange per bin, everyone
-// else sees the 1 with a plain load.  Every toucher also adds to the bin's load estimate (binned triangle refs +
-// kLargeWeight per large triangle) with a fire-and-forget reduction; order_kernel sorts the list by it.
+// Every toucher of a bin adds to the bin's load estimate (binned triangle refs + kLargeWeight per large triangle) with
+// a fire-and-forget reduction: a non-zero load marks the bin as non-empty, and its class orders the raster work.
 constexpr unsigned kLargeWeight = 16u;
-__device__ __forceinline__ void mark_tile(WorkCtl* ctl, unsigned* flags, unsigned* loads, unsigned* worklist, unsigned b, unsigned nt,
-                                          unsigned tile, unsigned weight) {
-    const size_t i = (size_t)b * nt + tile;
-    if (flags[i] == 0u && atomicExch(flags + i, 1u) == 0u) worklist[atomicAdd(&ctl->n_work, 1u)] = b * nt + tile;
-    atomicAdd(loads + i, weight);
+__device__ __forceinline__ void mark_tile(unsigned* loads, unsigned b, unsigned nt, unsigned tile, unsigned weight) {
+    atomicAdd(loads + (size_t)b * nt + tile, weight);
+}
+
+// work item r of the concatenated bucket lists; s_prefix[k] = number of items in buckets < k (kBuckets + 1 entries)
+__device__ __forceinline__ unsigned bucket_entry(const unsigned* s_prefix, const unsigned* __restrict__ buckets, size_t cap, unsigned r) {
+    int k = 0;
+#pragma unroll
+    for (int step = kBuckets / 2; step > 0; step >>= 1)
+        if (s_prefix[k + step] <= r) k += step;
+    return __ldcg(buckets + (size_t)k * cap + (r - s_prefix[k]));
+}
+
+// first warp of a CTA: bucket counts -> exclusive prefix in shared memory (s_prefix[kBuckets] = number of work items)
+__device__ __forceinline__ void load_bucket_prefix(const WorkCtl* __restrict__ ctl, unsigned* s_prefix) {
+    static_assert(kBuckets <= 32, "one warp scans the bucket counts");
+    const int lane = threadIdx.x;
+    if (lane < 32) {
+        const unsigned c = lane < kBuckets ? __ldcg(&ctl->bucket_cnt[lane]) : 0u;
+        unsigned incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane < kBuckets) s_prefix[lane + 1] = incl;
+        if (lane == 0) s_prefix[0] = 0u;
+    }
 }
 
 // One CTA = kSetupThreads consecutive triangles of one image.  Survivors that touch at most 2x2 tiles are
@@ -61,7 +83,7 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
              float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_cnt, unsigned* __restrict__ large_tri,
              int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs,
-             WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ loads, unsigned* __restrict__ worklist) {
+             WorkCtl* __restrict__ ctl, unsigned* __restrict__ loads, unsigned* __restrict__ buckets) {
     __shared__ unsigned s_cnt[kMaxBinTiles];
     __shared__ __align__(16) unsigned char s_refs[4 * kSetupThreads];
     __shared__ unsigned s_total;
@@ -150,11 +172,10 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         if (large) {
             large_tri[(size_t)b * maxT + (size_t)blockIdx.x * kSetupThreads + base + __popc(m & ((1u << lane) - 1u))] = (unsigned)t;
             for (int ty = ty0; ty <= ty1; ++ty)
-                for (int tx = tx0; tx <= tx1; ++tx) mark_tile(ctl, flags, loads, worklist, (unsigned)b, (unsigned)tg.nt, (unsigned)(ty * tg.ntx + tx), kLargeWeight);
+                for (int tx = tx0; tx <= tx1; ++tx) mark_tile(loads, (unsigned)b, (unsigned)tg.nt, (unsigned)(ty * tg.ntx + tx), kLargeWeight);
         }
     }
-    if (!tg.binned) return;   // CTA-uniform
-    __syncthreads();
+    if (tg.binned) {   // CTA-uniform (s_cnt is complete: the barrier above came after the counting atomics)
     // exclusive scan of s_cnt[0..nt) -> s_off: thread i owns items [i*per, (i+1)*per)
     const int per = (tg.nt + kSetupThreads - 1) / kSetupThreads;
     const int i_lo = min(tid * per, tg.nt), i_hi = min(i_lo + per, tg.nt);
@@ -175,7 +196,7 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         const unsigned c = s_cnt[i];
         s_off[i] = run;
         dimg[(size_t)i * tg.ncta_max] = (run << 16) | c;    // offset <= 1024, count <= 256
-        if (c) mark_tile(ctl, flags, loads, worklist, (unsigned)b, (unsigned)tg.nt, (unsigned)i, c);
+        if (c) mark_tile(loads, (unsigned)b, (unsigned)tg.nt, (unsigned)i, c);
         run += c;
     }
     if (tid == kSetupThreads - 1) s_total = run;          // this thread owns the last bins: run = all refs of the CTA
@@ -192,6 +213,24 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         const int n16 = ((int)s_total + 15) >> 4;
         if (tid < n16) region[tid] = reinterpret_cast<const uint4*>(s_refs)[tid];     // <= 64 stores of 16 B
     }
+    }
+    // ---- image completion: the CTA that finishes an image last publishes the image's non-empty bins by load class ----
+    __shared__ unsigned s_last;
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = (atomicAdd(&stats[b].ndone, 1u) == (unsigned)((T + kSetupThreads - 1) / kSetupThreads) - 1u) ? 1u : 0u;
+    __syncthreads();
+    if (s_last) {      // CTA-uniform
+        __threadfence();
+        const size_t cap = (size_t)gridDim.y * tg.nt;
+        for (int i = tid; i < tg.nt; i += kSetupThreads) {
+            const unsigned ld = __ldcg(loads + (size_t)b * tg.nt + i);
+            if (ld) {
+                const unsigned k = (unsigned)(kBuckets - 1) - min(ld >> kBucketShift, (unsigned)(kBuckets - 1));
+                buckets[k * cap + atomicAdd(&ctl->bucket_cnt[k], 1u)] = (unsigned)b * (unsigned)tg.nt + (unsigned)i;
+            }
+        }
+    }
 }
 
 __global__ void __launch_bounds__(kSetupThreads)
@@ -199,59 +238,9 @@ setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids
              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
              float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_cnt, unsigned* __restrict__ large_tri,
              int4* __restrict__ recs, unsigned* __restrict__ desc, unsigned char* __restrict__ refs,
-             WorkCtl* __restrict__ ctl, unsigned* __restrict__ flags, unsigned* __restrict__ loads, unsigned* __restrict__ worklist) {
+             WorkCtl* __restrict__ ctl, unsigned* __restrict__ loads, unsigned* __restrict__ buckets) {
     RAC_TL(1);
     setup_body(table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, znear, stats, large_cnt, large_tri, recs, desc, refs, ctl,
-               flags, loads, worklist);
+               loads, buckets);
     RAC_TL(1);
-}
-
-// One CTA orders the work list by decreasing load estimate (counting sort into 128 buckets): the persistent raster
-// CTAs then start with the heaviest bins and finish with the lightest, which keeps the tail of raster_kernel short
-// when there are only a few bins per CTA (2 400 bins over 592 CTAs at the bench workload: the mean CTA used to sit
-// idle for the last quarter of the kernel).  Lists longer than kOrderMax are left as they are: with that many items
-// per CTA the order does not matter.
-constexpr unsigned kOrderMax = 16384;
-constexpr int kOrderThreads = 1024;
-__global__ void __launch_bounds__(kOrderThreads)
-order_kernel(WorkCtl* __restrict__ ctl, const unsigned* __restrict__ loads, const unsigned* __restrict__ worklist,
-             unsigned* __restrict__ worklist_sorted) {
-    __shared__ unsigned s_hist[128];
-    const unsigned n = ctl->n_work;
-    if (n > kOrderMax) return;
-    const int tid = threadIdx.x;
-    if (tid < 128) s_hist[tid] = 0u;
-    __syncthreads();
-    unsigned e[kOrderMax / kOrderThreads], bk[kOrderMax / kOrderThreads];
-#pragma unroll
-    for (int k = 0; k < (int)(kOrderMax / kOrderThreads); ++k) {
-        const unsigned i = (unsigned)tid + (unsigned)k * kOrderThreads;
-        if (i < n) {
-            e[k] = worklist[i];
-            bk[k] = 127u - min(loads[e[k]] >> 3, 127u);                   // bucket 0 = heaviest
-            atomicAdd(&s_hist[bk[k]], 1u);
-        }
-    }
-    __syncthreads();
-    if (tid < 32) {        // exclusive scan of the 128 bucket sizes -> bucket cursors
-        unsigned v[4], sum = 0;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { v[k] = s_hist[4 * tid + k]; sum += v[k]; }
-        unsigned incl = sum;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const unsigned u = __shfl_up_sync(0xffffffffu, incl, o);
-            if (tid >= o) incl += u;
-        }
-        unsigned run = incl - sum;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { s_hist[4 * tid + k] = run; run += v[k]; }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int k = 0; k < (int)(kOrderMax / kOrderThreads); ++k) {
-        const unsigned i = (unsigned)tid + (unsigned)k * kOrderThreads;
-        if (i < n) worklist_sorted[atomicAdd(&s_hist[bk[k]], 1u)] = e[k];
-    }
-    if (tid == 0) ctl->ordered = 1u;
 }

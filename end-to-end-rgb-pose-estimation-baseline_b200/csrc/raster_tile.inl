@@ -561,7 +561,7 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
     }
 }
 
-// Persistent CTAs (SMs x resident CTAs) pop non-empty bins from the flat work list setup_kernel built.  The claim for
+// Persistent CTAs (SMs x resident CTAs) pop non-empty bins from the bucket lists setup_kernel built (heaviest first).  The claim for
 // the NEXT item is issued before the current bin is rasterised, so the atomic's round trip to L2 hides behind the bin.
 // (kRasterRegs = 56: 4 CTAs/SM leave 8 K registers, one resident gt_norm CTA of 256 threads x 32 registers per SM.)
 constexpr int kRasterRegs = 56;
@@ -570,16 +570,16 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
               const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
               SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_cnt,
               const unsigned* __restrict__ large_tri, const int4* __restrict__ recs, const unsigned* __restrict__ desc,
-              const unsigned char* __restrict__ refs, WorkCtl* __restrict__ ctl, const unsigned* __restrict__ worklist_any,
-              const unsigned* __restrict__ worklist_sorted, unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, unsigned* __restrict__ scratch_col) {
+              const unsigned char* __restrict__ refs, WorkCtl* __restrict__ ctl, const unsigned* __restrict__ buckets,
+              size_t bucket_cap, unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, unsigned* __restrict__ scratch_col) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RasterSmem& sm = *reinterpret_cast<RasterSmem*>(smem_raw);
     __shared__ int s_ctl[2];
     __shared__ unsigned s_item;
     __shared__ unsigned s_scan[3 * kRasterThreads + kRasterWarpsN];
     __shared__ ShadeCtx s_sc;
-    const unsigned n_work = __ldcg(&ctl->n_work);    // final: written by setup_kernel (previous launch)
-    const unsigned* worklist = __ldcg(&ctl->ordered) ? worklist_sorted : worklist_any;
+    __shared__ unsigned s_prefix[kBuckets + 1];
+    load_bucket_prefix(ctl, s_prefix);               // final: written by setup_kernel (previous launch)
     unsigned* my_scratch = scratch_col + (size_t)blockIdx.x * kScratchPerCta;
 #ifdef RAC_PHASE_TIMING
     WorkCtl* g_phase_ctl = ctl;
@@ -595,12 +595,13 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
 #endif
     if (threadIdx.x == 0) { s_item = atomicAdd(&ctl->next, 1u); s_ctl[0] = 0; s_ctl[1] = 0; }
     __syncthreads();
+    const unsigned n_work = s_prefix[kBuckets];
     for (;;) {
         const unsigned r = s_item;
         if (r >= n_work) break;
         unsigned r_next = 0;
         if (threadIdx.x == 0) r_next = atomicAdd(&ctl->next, 1u);   // consumed after the bin
-        const unsigned e = worklist[r];                               // image * nt + bin
+        const unsigned e = bucket_entry(s_prefix, buckets, bucket_cap, r);   // image * nt + bin, heaviest class first
         RAC_PHASE(0);
         raster_tile(sm, s_ctl, s_scan, &s_sc, my_scratch, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_cnt,
                     large_tri, recs, desc, refs, rgba_out, depth_out, (int)(e / (unsigned)tg.nt), (int)(e % (unsigned)tg.nt) RAC_PHASE_PASS);

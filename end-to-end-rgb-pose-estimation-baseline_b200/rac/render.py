@@ -36,6 +36,35 @@ def _scene_struct(scene):
     return ctypes.byref(s)
 
 
+_ids_cache = {}
+
+
+def _resolve_meshes(meshes, B):
+    """-> (ctypes int array of B handles, max triangle count).  One cache lookup per DISTINCT mesh of the batch (the
+    reference passes B path strings, usually all equal: data_loaders.py:100-118)."""
+    if not isinstance(meshes, (list, tuple)):
+        meshes = [meshes] * B
+    assert len(meshes) == B
+    seen = {}
+    handles = []
+    for m in meshes:
+        k = m if isinstance(m, str) else id(m)
+        dm = seen.get(k)
+        if dm is None:
+            dm = seen[k] = device_mesh(m)
+        handles.append(dm.handle)
+    maxT = max(dm.T for dm in seen.values())
+    if len(seen) == 1:
+        key = (handles[0], B)
+        ids = _ids_cache.get(key)
+        if ids is None:
+            if len(_ids_cache) > 256:
+                _ids_cache.clear()
+            ids = _ids_cache[key] = (ctypes.c_int * B)(*handles)
+        return ids, maxT
+    return (ctypes.c_int * B)(*handles), maxT
+
+
 def _prep(T_CO, K, meshes):
     dev = _lib.require_cuda()
     T = torch.as_tensor(T_CO).to(device=dev, dtype=torch.float32).contiguous()
@@ -43,12 +72,7 @@ def _prep(T_CO, K, meshes):
     B = T.shape[0]
     assert T.shape == (B, 4, 4)
     assert Kt.shape == (B, 3, 3)
-    if not isinstance(meshes, (list, tuple)):
-        meshes = [meshes] * B
-    assert len(meshes) == B
-    dms = [device_mesh(m) for m in meshes]
-    ids = (ctypes.c_int * B)(*[d.handle for d in dms])
-    maxT = max(d.T for d in dms)
+    ids, maxT = _resolve_meshes(meshes, B)
     return dev, T, Kt, B, ids, maxT
 
 
@@ -102,20 +126,45 @@ def render_concat_device(T_CO, meshes, K, img_size, gt_hwc, use_norm_depth=False
     return x, depth, rgb
 
 
-def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
-    """prepare_model_input on renders that already exist (iteration 0): -> x (B,C,H,W) f32 CUDA."""
-    L = _lib.lib()
-    dev = _lib.require_cuda()
-    init = torch.as_tensor(init_hwc).to(device=dev, dtype=torch.float32).contiguous()
-    gt = torch.as_tensor(gt_hwc).to(device=dev, dtype=torch.float32).contiguous()
-    B, H, W, _ = init.shape
-    assert init.shape == (B, H, W, 3) and gt.shape == (B, H, W, 3)
-    d = None
-    if use_norm_depth:
-        d = torch.as_tensor(depth).to(device=dev, dtype=torch.float32).contiguous()
-        assert d.shape == (B, H, W)
-    C = 7 if use_norm_depth else 6
-    x = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
+# ---- host gt crops: chunked upload on a copy stream, overlapped with the render ------------------------------
+# The reference's caller hands prepare_model_input HOST arrays (train_model.py:243).  The gt crop is the one large
+# input of a step (12 B/px); a plain `.to(device)` would queue its H2D copy behind the rasteriser on the current
+# stream and block the host.  Instead the copy runs in chunks of images on a library-owned copy stream while the
+# current stream is still rasterising, and each chunk is normalised + concatenated as soon as it has landed.
+_copy_streams = {}
+_gt_rings = {}
+_GT_RING = 2
+_GT_CHUNKS = 4
+
+
+def _copy_stream(dev):
+    s = _copy_streams.get(dev.index)
+    if s is None:
+        s = torch.cuda.Stream(device=dev)
+        _copy_streams[dev.index] = s
+    return s
+
+
+def _gt_staging(dev, shape):
+    """Ring of device staging buffers for uploaded gt crops; each entry carries the event of its last consumer."""
+    key = (dev.index, tuple(shape))
+    ring = _gt_rings.get(key)
+    if ring is None:
+        ring = {"next": 0, "bufs": [None] * _GT_RING, "done": [None] * _GT_RING}
+        _gt_rings[key] = ring
+    i = ring["next"]
+    ring["next"] = (i + 1) % _GT_RING
+    if ring["bufs"][i] is None:
+        ring["bufs"][i] = torch.empty(shape, dtype=torch.float32, device=dev)
+    return ring, i
+
+
+def _overlappable(t):
+    return (isinstance(t, torch.Tensor) and t.device.type == "cpu" and t.dtype == torch.float32 and t.is_contiguous()
+            and t.dim() == 4 and t.is_pinned() and not torch.cuda.is_current_stream_capturing())
+
+
+def _assemble_call(L, init, gt, d, B, W, H, use_norm_depth, x, dev):
     need = L.rac_assemble_workspace_bytes(B)
     ws = _workspace(dev, need)
     base = (ws.data_ptr() + 255) // 256 * 256
@@ -123,6 +172,47 @@ def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
                               _lib.ptr(x), ctypes.c_void_p(base), ws.numel() - (base - ws.data_ptr()),
                               _lib.stream_ptr())
     _lib.check(rc)
+
+
+def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
+    """prepare_model_input on renders that already exist (iteration 0): -> x (B,C,H,W) f32 CUDA."""
+    L = _lib.lib()
+    dev = _lib.require_cuda()
+    init = torch.as_tensor(init_hwc).to(device=dev, dtype=torch.float32).contiguous()
+    B, H, W, _ = init.shape
+    assert init.shape == (B, H, W, 3) and tuple(gt_hwc.shape) == (B, H, W, 3)
+    d = None
+    if use_norm_depth:
+        d = torch.as_tensor(depth).to(device=dev, dtype=torch.float32).contiguous()
+        assert d.shape == (B, H, W)
+    C = 7 if use_norm_depth else 6
+    x = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
+    if _overlappable(gt_hwc) and B >= 2 * _GT_CHUNKS:
+        main = torch.cuda.current_stream(dev)
+        cs = _copy_stream(dev)
+        ring, slot = _gt_staging(dev, (B, H, W, 3))
+        gt = ring["bufs"][slot]
+        if ring["done"][slot] is not None:
+            cs.wait_event(ring["done"][slot])          # the staging buffer's previous consumer has finished
+        per = (B + _GT_CHUNKS - 1) // _GT_CHUNKS
+        events = []
+        with torch.cuda.stream(cs):
+            for b0 in range(0, B, per):
+                b1 = min(B, b0 + per)
+                gt[b0:b1].copy_(gt_hwc[b0:b1], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(cs)
+                events.append((b0, b1, ev))
+        for b0, b1, ev in events:
+            main.wait_event(ev)
+            _assemble_call(L, init[b0:b1], gt[b0:b1], d[b0:b1] if d is not None else None, b1 - b0, W, H,
+                           use_norm_depth, x[b0:b1], dev)
+        done = torch.cuda.Event()
+        done.record(main)
+        ring["done"][slot] = done
+        return x
+    gt = torch.as_tensor(gt_hwc).to(device=dev, dtype=torch.float32).contiguous()
+    _assemble_call(L, init, gt, d, B, W, H, use_norm_depth, x, dev)
     return x
 
 

@@ -39,11 +39,11 @@ def main():
         ws = max(R._ws_cache.values(), key=lambda w: w.numel())
         base = (ws.data_ptr() + 255) // 256 * 256 - ws.data_ptr()
         off = base + (64 * B + 255) // 256 * 256            # WorkCtl follows the ImgStats block
-        ctl = ws[off:off + 256].cpu().numpy().view(np.uint32)
+        ctl = ws[off:off + 512].cpu().numpy().view(np.uint32)
         pad = ctl[2:64].copy().view(np.uint64)
         if it >= 2:
             tot += pad.astype(np.float64)
-        print("n_work", ctl[0])
+        print("n_work", int(ctl[64:80].sum()), "by load class (heaviest first):", ctl[64:80].tolist())
     s = tot[:len(NAMES)].sum()
     for n, v in zip(NAMES, tot):
         print("%-28s %6.2f%%  %10.0f cycles/iter" % (n, 100 * v / s, v / 4))

@@ -190,6 +190,25 @@ def test_assemble_input_only(rac, use_depth):
     np.testing.assert_allclose(c, ref, rtol=1e-5, atol=2e-5)
 
 
+@pytest.mark.parametrize("B,use_depth", [(8, False), (13, True), (64, False)])
+def test_assemble_input_pinned_gt_overlapped_upload(rac, B, use_depth):
+    """A pinned host gt crop takes the chunked copy-stream upload (rac/render.py); the result must be bit-identical
+    to the plain path, for ragged chunk sizes and across staging-ring reuse."""
+    rng = np.random.default_rng(5 + B)
+    H, W = 48, 64
+    init = torch.tensor(rng.uniform(0, 1, (B, H, W, 3)).astype(np.float32), device="cuda")
+    depth = torch.tensor(np.where(rng.uniform(size=(B, H, W)) > 0.5, rng.uniform(2.2, 2.8, (B, H, W)), 0).astype(np.float32),
+                         device="cuda")
+    for rep in range(5):                 # > ring depth: the staging buffers are reused
+        gt = (rng.integers(0, 256, (B, H, W, 3)) / 255.0).astype(np.float32)
+        plain = rac.assemble_input_device(init, gt, depth, use_depth)               # numpy -> ordinary .to(device)
+        pinned = torch.tensor(gt).pin_memory()
+        over = rac.assemble_input_device(init, pinned, depth, use_depth)
+        assert torch.equal(plain, over), rep
+        ref = assemble_ref.prepare_model_input(init.cpu().numpy(), gt.astype(np.float64), depth.cpu().numpy(), use_depth).numpy()
+        np.testing.assert_allclose(over.cpu().numpy(), ref, rtol=1e-5, atol=2e-5)
+
+
 def test_reference_api_modules(rac, tmp_path):
     """The drop-in modules: renderer.render_scene, data_loaders.render_batch / prepare_model_input."""
     import data_loaders
