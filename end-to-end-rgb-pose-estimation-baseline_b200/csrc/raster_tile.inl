@@ -266,7 +266,7 @@ template <bool FINAL>
 __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const BinCtx& bc,
                                             unsigned* __restrict__ scratch_col, const ShadeCtx* s_sc,
                                             const SceneConsts& S, unsigned* __restrict__ rgba_out,
-                                            float* __restrict__ depth_out, size_t img_pix, int W, TileAcc& acc
+                                            float* __restrict__ depth_out, size_t img_pix, int W, TileAcc& acc, int need_dstats
                                             RAC_PHASE_ARGS) {
     const int tid = threadIdx.x, lane = tid & 31;
     const int tw = bc.x_hi - bc.x_lo + 1, th = bc.y_hi - bc.y_lo + 1;
@@ -378,8 +378,10 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
         if (k[0] != kKeyEmpty32) depth = depth_readback(k[0] >> 8, S);
         depth_out[o] = depth;
         acc.qmax = max(acc.qmax, max(r8, max(g8, b8)));
-        acc.dmax = fmaxf(acc.dmax, depth);
-        if (depth > 0.01f) { acc.dcount++; acc.dsum += (double)depth; acc.dsumsq += (double)depth * (double)depth; }
+        if (need_dstats) {      // normalize_depth statistics: only when the caller asked for the normalised depth plane
+            acc.dmax = fmaxf(acc.dmax, depth);
+            if (depth > 0.01f) { acc.dcount++; acc.dsum += (double)depth; acc.dsumsq += (double)depth * (double)depth; }
+        }
     }
 }
 
@@ -387,7 +389,7 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
 __device__ __noinline__ void commit_bin(RasterSmem& sm, int* q_count, const BinCtx& bc, unsigned* __restrict__ scratch_col,
                                         const ShadeCtx* s_sc, const SceneConsts& S RAC_PHASE_ARGS) {
     TileAcc dummy;
-    resolve_bin<false>(sm, q_count, bc, scratch_col, s_sc, S, nullptr, nullptr, 0, 0, dummy RAC_PHASE_PASS);
+    resolve_bin<false>(sm, q_count, bc, scratch_col, s_sc, S, nullptr, nullptr, 0, 0, dummy, 0 RAC_PHASE_PASS);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -403,7 +405,9 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
                                             const unsigned* __restrict__ large_tri, const int4* __restrict__ recs,
                                             const unsigned* __restrict__ desc, const unsigned char* __restrict__ refs,
                                             unsigned* __restrict__ rgba_out, float* __restrict__ depth_out,
-                                            int b, int tile RAC_PHASE_ARGS) {
+                                            int b, int tile, unsigned r_next, unsigned n_work, const unsigned* s_prefix,
+                                            const unsigned* __restrict__ buckets, size_t bucket_cap, unsigned* s_next,
+                                            int need_dstats RAC_PHASE_ARGS) {
     int* q_count = s_ctl, *med_count = s_ctl + 1;
     unsigned* s_dcnt = s_scan;                      // [kRasterThreads] descriptor counts (large pass: per-CTA counts)
     unsigned* s_dscan = s_scan + kRasterThreads;    // [kRasterThreads] exclusive scan
@@ -472,15 +476,20 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
             __syncthreads();
             const int nd = min(kRasterThreads, ncta - dbase);
             for (unsigned base = 0; base < total; base += kQueueCap) {
-                // expand refs [base, base + kQueueCap) of this descriptor group into the queue, one warp per descriptor
-                for (int jj = warp; jj < nd; jj += kRasterWarpsN) {
-                    const unsigned cj = s_dcnt[jj];
-                    if (cj == 0) continue;
-                    const unsigned sj = s_dscan[jj];
-                    const unsigned lo = max(sj, base), hi = min(sj + cj, base + (unsigned)kQueueCap);
-                    const unsigned char* region = refs + (((size_t)b * tg.ncta_max + dbase + jj) << 10) + s_doff[jj];
-                    for (unsigned k = lo + lane; k < hi; k += 32)
-                        sm.queue[k - base] = (dbase + jj) * kSetupThreads + (int)region[k - sj];
+                // expand refs [base, base + kQueueCap) of this descriptor group into the queue: one thread per ref, which
+                // finds its descriptor by binary search in the scanned counts — every ref byte of the bin is requested
+                // in the same L2 round trip (a warp walking its descriptors one after the other paid one trip each)
+                {
+                    const unsigned qn = min((unsigned)kQueueCap, total - base);
+                    const int top = 1 << (31 - __clz(max(nd - 1, 1)));
+                    for (unsigned q = (unsigned)tid; q < qn; q += kRasterThreads) {
+                        const unsigned g = base + q;
+                        int jj = 0;
+                        for (int step = top; step > 0; step >>= 1)
+                            if (jj + step < nd && s_dscan[jj + step] <= g) jj += step;     // last descriptor starting at or before g
+                        const unsigned char* region = refs + (((size_t)b * tg.ncta_max + dbase + jj) << 10) + s_doff[jj];
+                        sm.queue[q] = (dbase + jj) * kSetupThreads + (int)region[g - s_dscan[jj]];
+                    }
                 }
                 __syncthreads();
                 RAC_PHASE(1);
@@ -530,18 +539,36 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
     }
 
     RAC_PHASE(5);
+    // The ticket of the next bin was claimed when this one started, so it has long arrived: park it in shared memory and
+    // fetch its work-list entry with an asynchronous 4-byte copy that lands during the resolve (nothing of either is
+    // held in registers across the shading loop, and the L2 round trip is off the hand-over path).
+    if (tid == 0) {
+        s_next[0] = r_next;
+        if (r_next < n_work) {
+            int k = 0;
+#pragma unroll
+            for (int step = kBuckets / 2; step > 0; step >>= 1)
+                if (s_prefix[k + step] <= r_next) k += step;
+            const unsigned* src = buckets + (size_t)k * bucket_cap + (r_next - s_prefix[k]);
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(s_next + 1);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(dst), "l"(src) : "memory");
+        }
+    }
     // ---- resolve + shade + write, and per-image accumulators ----
     TileAcc acc;
     acc.qmax = 0; acc.dcount = 0; acc.dmax = 0.0f; acc.dsum = 0.0; acc.dsumsq = 0.0;
-    resolve_bin<true>(sm, q_count, bc, scratch_col, s_sc, S, rgba_out, depth_out, img_pix, W, acc RAC_PHASE_PASS);
+    resolve_bin<true>(sm, q_count, bc, scratch_col, s_sc, S, rgba_out, depth_out, img_pix, W, acc, need_dstats RAC_PHASE_PASS);
     RAC_PHASE(10);
     // block reduction -> one atomic per accumulator per CTA
     __shared__ double red_d[2][kRasterWarpsN];
     __shared__ unsigned red_u[3][kRasterWarpsN];
     acc.qmax = warp_max(acc.qmax);
-    acc.dcount = (unsigned)__reduce_add_sync(0xffffffffu, acc.dcount);
-    const unsigned dmax_bits = warp_max(__float_as_uint(acc.dmax));
-    acc.dsum = warp_sum(acc.dsum); acc.dsumsq = warp_sum(acc.dsumsq);
+    unsigned dmax_bits = 0u;
+    if (need_dstats) {      // kernel-uniform
+        acc.dcount = (unsigned)__reduce_add_sync(0xffffffffu, acc.dcount);
+        dmax_bits = warp_max(__float_as_uint(acc.dmax));
+        acc.dsum = warp_sum(acc.dsum); acc.dsumsq = warp_sum(acc.dsumsq);
+    }
     if (lane == 0) {
         red_u[0][warp] = acc.qmax; red_u[1][warp] = acc.dcount; red_u[2][warp] = dmax_bits;
         red_d[0][warp] = acc.dsum; red_d[1][warp] = acc.dsumsq;
@@ -571,11 +598,12 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
               SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_cnt,
               const unsigned* __restrict__ large_tri, const int4* __restrict__ recs, const unsigned* __restrict__ desc,
               const unsigned char* __restrict__ refs, WorkCtl* __restrict__ ctl, const unsigned* __restrict__ buckets,
-              size_t bucket_cap, unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, unsigned* __restrict__ scratch_col) {
+              size_t bucket_cap, unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, unsigned* __restrict__ scratch_col,
+              int need_dstats) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RasterSmem& sm = *reinterpret_cast<RasterSmem*>(smem_raw);
     __shared__ int s_ctl[2];
-    __shared__ unsigned s_item;
+    __shared__ unsigned s_next[2];     // ticket and work-list entry of the CTA's next bin
     __shared__ unsigned s_scan[3 * kRasterThreads + kRasterWarpsN];
     __shared__ ShadeCtx s_sc;
     __shared__ unsigned s_prefix[kBuckets + 1];
@@ -593,22 +621,34 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
         atomicAdd(&g_tl[9], t - g_tl[15]);
     }
 #endif
-    if (threadIdx.x == 0) { s_item = atomicAdd(&ctl->next, 1u); s_ctl[0] = 0; s_ctl[1] = 0; }
+    // The first ticket is the CTA's own index (no atomic before the first bin); later tickets come from the counter.
+    if (threadIdx.x == 0) { s_ctl[0] = 0; s_ctl[1] = 0; }
     __syncthreads();
     const unsigned n_work = s_prefix[kBuckets];
-    for (;;) {
-        const unsigned r = s_item;
-        if (r >= n_work) break;
+    unsigned r = blockIdx.x;
+    unsigned e = r < n_work ? bucket_entry(s_prefix, buckets, bucket_cap, r) : 0u;   // image * nt + bin, heaviest class first
+    while (r < n_work) {
+#ifdef RAC_PHASE_TIMING
+        const long long t_bin0 = clock64();
+#endif
         unsigned r_next = 0;
-        if (threadIdx.x == 0) r_next = atomicAdd(&ctl->next, 1u);   // consumed after the bin
-        const unsigned e = bucket_entry(s_prefix, buckets, bucket_cap, r);   // image * nt + bin, heaviest class first
+        if (threadIdx.x == 0) r_next = gridDim.x + atomicAdd(&ctl->next, 1u);   // parked in s_next before the resolve
         RAC_PHASE(0);
         raster_tile(sm, s_ctl, s_scan, &s_sc, my_scratch, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_cnt,
-                    large_tri, recs, desc, refs, rgba_out, depth_out, (int)(e / (unsigned)tg.nt), (int)(e % (unsigned)tg.nt) RAC_PHASE_PASS);
+                    large_tri, recs, desc, refs, rgba_out, depth_out, (int)(e / (unsigned)tg.nt), (int)(e % (unsigned)tg.nt),
+                    r_next, n_work, s_prefix, buckets, bucket_cap, s_next, need_dstats RAC_PHASE_PASS);
         RAC_PHASE(11);
-        __syncthreads();                  // every thread has read s_item (and left the bin's shared memory)
-        if (threadIdx.x == 0) s_item = r_next;
-        __syncthreads();
+        if (threadIdx.x == 0) asm volatile("cp.async.wait_all;" ::: "memory");
+        __syncthreads();                  // the bin's shared memory is free; thread 0's copy has landed
+#ifdef RAC_PHASE_TIMING
+        if (threadIdx.x == 0) {           // cycles per load class: u64 slots 14..29 of WorkCtl::pad
+            int k = 0;
+            for (int step = kBuckets / 2; step > 0; step >>= 1)
+                if (s_prefix[k + step] <= r) k += step;
+            atomicAdd(reinterpret_cast<unsigned long long*>(ctl->pad) + 14 + k, (unsigned long long)(clock64() - t_bin0));
+        }
+#endif
+        r = s_next[0]; e = s_next[1];     // (s_next is rewritten only after the next bin's coverage barriers)
         RAC_PHASE(12);
     }
 #ifdef RAC_PHASE_TIMING

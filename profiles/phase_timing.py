@@ -33,6 +33,7 @@ def main():
     B, W, H = bench.B, bench.W, bench.H
     gt = torch.rand((B, H, W, 3), device="cuda")
     tot = np.zeros(31, dtype=np.float64)
+    cls_n = np.zeros(16, dtype=np.float64)
     for it in range(6):
         rac.render_concat_device(sets[it % len(sets)]["T_init"], mesh, K, (W, H), gt)
         torch.cuda.synchronize()
@@ -43,11 +44,21 @@ def main():
         pad = ctl[2:64].copy().view(np.uint64)
         if it >= 2:
             tot += pad.astype(np.float64)
+        if it >= 2:
+            cls_n += ctl[64:80].astype(np.float64)
         print("n_work", int(ctl[64:80].sum()), "by load class (heaviest first):", ctl[64:80].tolist())
     s = tot[:len(NAMES)].sum()
     for n, v in zip(NAMES, tot):
         print("%-28s %6.2f%%  %10.0f cycles/iter" % (n, 100 * v / s, v / 4))
+    return tot, cls_n
+
+
+def per_class(tot, cls_n):
+    print("bin duration by load class (class k: load in [32 (15-k), 32 (16-k)) refs; thread-0 cycles per bin, 4 CTAs/SM co-resident)")
+    for k in range(16):
+        if cls_n[k] > 0:
+            print("  class %2d  bins/iter %6.1f   cycles/bin %8.0f" % (k, cls_n[k] / 4, tot[14 + k] / cls_n[k]))
 
 
 if __name__ == "__main__":
-    main()
+    per_class(*main())
