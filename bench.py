@@ -16,7 +16,7 @@ For N>1 launch with torch.distributed.run (the driver does); weak scaling: every
 `value`   = renders/s with inputs resident in HBM (device-timed, CUDA events on the launching stream).
 `e2e`     = the same through the reference-facing Python API (data_loaders.render_batch /
             prepare_model_input / calculate_T_CO_pred / loss) with HOST (pinned) buffers in, host pose out.
-`roofline`= the rasterize+concat stage (setup + raster + finalize kernels of one rac_render_concat call),
+`roofline`= the rasterize+concat stage (setup + raster + gt_norm + finalize_live kernels of one rac_render_concat call),
             algorithmic bytes 36*W*H per image over its CUDA-event time.
 `--impl reference` times the CPU oracle (oracle/: C rasteriser restatement + reference-restated torch CPU
 pose/loss) on the host cores — the reference's own renderer needs OpenGL and is unavailable on this box.
@@ -261,6 +261,12 @@ def run_ours(args):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = None       # DRAM bytes per rac_render_concat call, from the committed ncu capture of this same command
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic_r01.json")) as f:
+            traffic = float(json.load(f)["stage_dram_bytes_per_call"])
+    except Exception:
+        pass
     achieved = algo_bytes / (stage_ms * 1e-3) / 1e9
     h2d = sum(dsets[0][k].numel() * 4 for k in ("h_gt", "h_T_init", "h_T_gt", "h_y", "h_pts"))
     out = {
@@ -271,9 +277,10 @@ def run_ours(args):
         "config": {"workload": workload_name(), "global_batch": world * B, "width": W, "height": H, "triangles": len(mesh.faces),
                    "rot_repr": ROT, "loss": LOSS, "points": NPTS, "parallelism": "dp%d (batch sharded, no data-path collective)" % world,
                    "l2": "rotating %d input/output sets (%.0f MB each) > 126 MB L2" % (NSETS, (36.0 * W * H * B) / 1e6)},
-        "roofline": {"bound": "hbm", "kernel": "rac_render_concat stage (assemble_stats + setup + raster + finalize_concat kernels), timed as its own graph replay",
+        "roofline": {"bound": "hbm", "kernel": "rac_render_concat stage (setup + raster + finalize_live kernels, gt_norm on a forked stream under them), timed as its own graph replay",
                      "achieved": achieved, "peak": peak, "peak_source": "measured" if peaks else "fallback",
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "traffic_source": "profiles/traffic_r01.json: ncu dram__bytes_read+write summed over the stage's 4 kernels, per call (serialised, so part of the 118 MB written is still dirty in the 126 MB L2 when the last kernel ends)",
                      "stage_ms": stage_ms, "algorithmic_bytes": algo_bytes,
                      "triangle_setup_rate_per_s": B * len(mesh.faces) / (stage_ms * 1e-3)},
         "e2e": {"value": world * B * args.steps / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms / args.steps,

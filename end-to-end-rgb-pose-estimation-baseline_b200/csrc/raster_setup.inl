@@ -233,7 +233,10 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
     }
 }
 
-__global__ void __launch_bounds__(kSetupThreads)
+#ifndef RAC_SETUP_MIN_CTAS
+#define RAC_SETUP_MIN_CTAS 5
+#endif
+__global__ void __launch_bounds__(kSetupThreads, RAC_SETUP_MIN_CTAS)
 setup_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
              const float* __restrict__ T_CO, const float* __restrict__ K, int W, int H, int maxT, TileGrid tg,
              float znear, ImgStats* __restrict__ stats, unsigned* __restrict__ large_cnt, unsigned* __restrict__ large_tri,
