@@ -381,6 +381,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~15 s CPU oracle leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
+        # torchrun exports OMP_NUM_THREADS=1 to every rank; the reference arm runs on rank 0 alone and is meant to use
+        # every host core, so undo that before libgomp is loaded (by torch / the oracle library)
+        os.environ["OMP_NUM_THREADS"] = str(len(os.sched_getaffinity(0)))
         run_reference(args)
     else:
         run_ours(args)

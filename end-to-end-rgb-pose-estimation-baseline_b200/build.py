@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librac_b200.so")
 STAMP = os.path.join(HERE, ".librac_b200.stamp")
-SOURCES = ["rac_api.cu", "raster.cu", "pose_update.cu", "add_loss.cu"]
+SOURCES = ["rac_api.cu", "raster.cu", "pose_update.cu", "add_loss.cu", "aux_kernels.cu"]
 HEADERS = ["rac_common.cuh", "raster.cuh", "raster_setup.inl", "raster_shade.inl", "raster_tile.inl", "raster_finalize.inl",
            os.path.join("..", "..", "include", "rac.h")]
 

@@ -67,6 +67,12 @@ def sample_T_CO_inits_and_gts(batch_size, scene_config):
     return np.array(inits, dtype=np.float32), np.array(gts, dtype=np.float32)
 
 
+def sample_T_CO_inits_and_gts_device(batch_size, scene_config, generator=None):
+    """The same distribution as sample_T_CO_inits_and_gts, composed for the whole batch by one kernel
+    (rac_sample_poses) from torch's device RNG: -> two (B,4,4) f32 CUDA tensors."""
+    return rac.sample_poses_device(batch_size, scene_config, generator=generator)
+
+
 def sample_verts_to_batch(mesh_paths, num_verts_to_sample):
     return torch.stack([sample_vertices_as_tensor(p, num_verts_to_sample) for p in mesh_paths])
 

@@ -56,6 +56,10 @@ SIGNATURES = {
     "rac_add_loss_bwd": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
     "rac_transform_pts_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "rac_transform_pts_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "rac_sample_poses": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_double, c_double, c_double,
+                                 c_void_p, c_void_p, c_void_p]),
+    "rac_silhouette": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "rac_blend": (c_int, [c_void_p, c_void_p, c_float, c_int, c_size_t, c_void_p, c_void_p]),
 }
 
 RAC_ROT = {"6D": 0, "SVD": 1, "3D": 2}

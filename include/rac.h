@@ -180,6 +180,31 @@ RAC_API int rac_transform_pts_fwd(const float* d_T, const float* d_pts, int B, i
 RAC_API int rac_transform_pts_bwd(const float* d_gout, const float* d_T, const float* d_pts,
                                   int B, int M, int N, float* d_gT, float* d_gpts, rac_stream_t stream);
 
+/* ---- §8(f) N3: batched pose sampling ---------------------------------------
+ * ref: se3_helpers.py:76-88 (get_T_CO_init_and_gt) with :39-74 (random rotation + translation, small perturbation,
+ * camera on +x looking at the origin), data_loaders.py:58-67 (sample_T_CO_inits_and_gts: a Python loop over B).
+ * The caller draws the variates the reference draws per sample, in the reference's order, and this call composes the
+ * two poses for the whole batch in one launch (f64 arithmetic like numpy, f32 row-major 4x4 out):
+ *   d_u01 (B,12) f32 uniforms in [0,1): [theta_gt, axis_gt x3, theta_delta, t_delta x3, axis_delta x3, cam distance]
+ *   d_n01 (B,3)  f32 standard normals:  gt translation
+ * distance / distance_dev / gt_transl_dev / transl_dev / angle_dev_deg: the scene_config entries
+ * (configs/example_config.py:45-52). */
+RAC_API int rac_sample_poses(const float* d_u01, const float* d_n01, int B, double distance, double distance_dev,
+                             double gt_transl_dev, double transl_dev, double angle_dev_deg,
+                             float* d_T_init, float* d_T_gt, rac_stream_t stream);
+
+/* ---- §8(f) N4: silhouette ring and overlay ----------------------------------
+ * ref: visualization.py:19-31 (create_silhouette): mask = mean(img,2) > 0; ring = clip(box5x5(mask),0,1) - mask with
+ * zero padding.  d_img_hwc (B,H,W,3) f32.  silhouette_only != 0: d_out (B,H,W) f32 ring mask; otherwise d_out
+ * (B,H,W,3) f32 = the image with ring pixels painted h_colour3 (host pointer to 3 floats, NULL = red (1,0,0)). */
+RAC_API int rac_silhouette(const float* d_img_hwc, int B, int W, int H, int silhouette_only, const float* h_colour3,
+                           float* d_out, rac_stream_t stream);
+/* ref: visualization.py:34-37 (blend_imgs): uint8(im*255) of both (truncation), PIL Image.blend
+ * (uint8)(a + alpha (b - a)), / 255.  n elements, f32 in and out.  quantized_inputs != 0: the inputs already hold the
+ * 8-bit codes 0..255 (the Python wrapper quantises f64 inputs on the host, in f64 as numpy would). */
+RAC_API int rac_blend(const float* d_im1, const float* d_im2, float alpha, int quantized_inputs, size_t n,
+                      float* d_out, rac_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif
