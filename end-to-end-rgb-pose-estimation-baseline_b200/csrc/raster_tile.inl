@@ -23,7 +23,7 @@
     do {                                                                                                        \
         if (threadIdx.x == 0) {                                                                                 \
             const long long _t = clock64();                                                                     \
-            atomicAdd(reinterpret_cast<unsigned long long*>(g_phase_ctl->pad) + (idx), (unsigned long long)(_t - g_phase_t)); \
+            if (g_phase_ctl) atomicAdd(reinterpret_cast<unsigned long long*>(g_phase_ctl->pad) + (idx), (unsigned long long)(_t - g_phase_t)); \
             g_phase_t = _t;                                                                                     \
         }                                                                                                       \
     } while (0)
@@ -630,6 +630,14 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
     while (r < n_work) {
 #ifdef RAC_PHASE_TIMING
         const long long t_bin0 = clock64();
+#ifdef RAC_PHASE_CLASS      // phase timeline of one load class only
+        {
+            int k = 0;
+            for (int step = kBuckets / 2; step > 0; step >>= 1)
+                if (s_prefix[k + step] <= r) k += step;
+            g_phase_ctl = (k == RAC_PHASE_CLASS) ? ctl : nullptr;
+        }
+#endif
 #endif
         unsigned r_next = 0;
         if (threadIdx.x == 0) r_next = gridDim.x + atomicAdd(&ctl->next, 1u);   // parked in s_next before the resolve
