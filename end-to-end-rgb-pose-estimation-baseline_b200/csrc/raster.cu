@@ -247,12 +247,19 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         if (rc != RAC_OK) return rc;
     }
     cudaStream_t sstream = (skip & 16) ? stream : side->stream;
+    const TileGrid tg = make_tile_grid(W, H, maxT);
+    // Concat-only calls (no depth / HWC / RGBA8 side outputs): the gt kernel leaves the quads of non-empty bins alone,
+    // so it and finalize_live_kernel write disjoint memory and the side stream is joined AFTER finalize — the gt
+    // kernel, which runs about as long as setup + raster, no longer sits in front of finalize on the critical path.
+    const bool late_join = d_gt_hwc && fin.x_nchw && !fin.depth_out && !fin.rgb_hwc_out && !fin.rgba_copy && !skip &&
+                           W % 4 == 0 && npix % 4 == 0 && aligned16(d_gt_hwc) && aligned16(fin.x_nchw);
     auto side_work = [&]() -> int {
         if (skip & 1) return RAC_OK;
         if (d_gt_hwc) {
             // one CTA per SM (n_sm / 8 clusters), launched before setup so that it is resident next to the
             // setup / raster CTAs for the whole call and streams in the background
-            int rc = launch_gt_norm(d_gt_hwc, fin.x_nchw, B, (int)npix, fin.use_norm_depth, 1, (skip & 64) ? 0 : n_sm / kGtCluster, sstream);
+            int rc = launch_gt_norm(d_gt_hwc, fin.x_nchw, B, (int)npix, fin.use_norm_depth, 1, (skip & 64) ? 0 : n_sm / kGtCluster, sstream,
+                                    late_join ? ws.loads : nullptr, W, tg.ntx, tg.nt);
             if (rc != RAC_OK) return rc;
         }
         if (fin.depth_out) RAC_CUDA_CHECK(cudaMemsetAsync(fin.depth_out, 0, sizeof(float) * npix * B, sstream));
@@ -281,7 +288,6 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         if (rc != RAC_OK) return rc;
         d_ids = ws.mesh_ids;
     }
-    const TileGrid tg = make_tile_grid(W, H, maxT);
     if (!(skip & 2)) {
         dim3 grid(tg.ncta_max, B);
         setup_kernel<<<grid, kSetupThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
@@ -308,7 +314,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
                                                                           (fin.x_nchw && fin.use_norm_depth) ? 1 : 0);
         RAC_LAUNCHED();
     }
-    if (!(skip & 16)) RAC_CUDA_CHECK(cudaStreamWaitEvent(stream, side->join, 0));
+    if (!(skip & 16) && !late_join) RAC_CUDA_CHECK(cudaStreamWaitEvent(stream, side->join, 0));
     if (!(skip & 8)) {
         fin.stats = ws.stats; fin.rgba = ws.rgba; fin.depth = ws.depth; fin.init_hwc = nullptr;
         fin.npix = (int)npix; fin.W = W;
@@ -318,6 +324,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         finalize_live_kernel<<<grid, kFinThreads, 0, stream>>>(fin, tg, H, ws.buckets, (size_t)B * tg.nt, ws.ctl);
         RAC_LAUNCHED();
     }
+    if (late_join) RAC_CUDA_CHECK(cudaStreamWaitEvent(stream, side->join, 0));
     return RAC_OK;
 }
 

@@ -242,7 +242,8 @@ constexpr int kGtCluster = 8;
 constexpr int kGtThreads = 256;
 
 __global__ void __launch_bounds__(kGtThreads, 8)
-gt_norm_kernel(const float* __restrict__ gt_hwc, float* __restrict__ x_nchw, int npix, int C, int ch0, int nzero, int vec, int B) {
+gt_norm_kernel(const float* __restrict__ gt_hwc, float* __restrict__ x_nchw, int npix, int C, int ch0, int nzero, int vec, int B,
+               const unsigned* __restrict__ live_loads, int W, int ntx, int nt) {
     namespace cg = cooperative_groups;
     cg::cluster_group cluster = cg::this_cluster();
     __shared__ double s_warp[2][kGtThreads / 32];
@@ -258,7 +259,18 @@ gt_norm_kernel(const float* __restrict__ gt_hwc, float* __restrict__ x_nchw, int
     // slice of this CTA, in quads of 4 pixels (vec) or in pixels
     const int nunit = vec ? npix >> 2 : npix;
     const int u0 = (int)((long long)nunit * rank / kGtCluster), u1 = (int)((long long)nunit * (rank + 1) / kGtCluster);
-    if (vec) {
+    if (vec && live_loads && nzero > 0) {
+        // live_loads (setup_kernel's per-bin load estimates, final before this kernel starts; W % 4 == 0): the quads
+        // of non-empty bins are left alone — finalize_live_kernel writes every pixel of those bins, so the two kernels
+        // touch disjoint parts of the render planes and need no ordering between them
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        const unsigned* ll = live_loads + (size_t)b * nt;
+        for (int q = u0 + tid; q < u1; q += kGtThreads) {
+            const int p = q << 2, y = p / W, x = p - y * W;
+            if (__ldg(ll + (y / kTileH) * ntx + x / kTileW) != 0u) continue;
+            for (int pl = 0; pl < nzero; ++pl) __stcs(reinterpret_cast<float4*>(x0 + (size_t)pl * npix) + q, z);
+        }
+    } else if (vec) {
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         for (int pl = 0; pl < nzero; ++pl)
             for (int q = u0 + tid; q < u1; q += kGtThreads) __stcs(reinterpret_cast<float4*>(x0 + (size_t)pl * npix) + q, z);
@@ -332,7 +344,7 @@ gt_norm_kernel(const float* __restrict__ gt_hwc, float* __restrict__ x_nchw, int
 
 // n_clusters: how many images are in flight at once (persistent clusters loop over the batch); <= 0 = one per image
 static int launch_gt_norm(const float* d_gt_hwc, float* d_x_nchw, int B, int npix, int use_norm_depth, int zero_render_planes,
-                          int n_clusters, cudaStream_t stream) {
+                          int n_clusters, cudaStream_t stream, const unsigned* d_live_loads = nullptr, int W = 0, int ntx = 0, int nt = 0) {
     const int C = use_norm_depth ? 7 : 6, ch0 = use_norm_depth ? 4 : 3;
     const int vec = (npix % 4 == 0 && (reinterpret_cast<uintptr_t>(d_gt_hwc) & 15u) == 0 &&
                      (reinterpret_cast<uintptr_t>(d_x_nchw) & 15u) == 0) ? 1 : 0;
@@ -352,7 +364,8 @@ static int launch_gt_norm(const float* d_gt_hwc, float* d_x_nchw, int B, int npi
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = kGtCluster; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr; cfg.numAttrs = 1;
-    RAC_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gt_norm_kernel, d_gt_hwc, d_x_nchw, npix, C, ch0, zero_render_planes ? ch0 : 0, vec, B));
+    RAC_CUDA_CHECK(cudaLaunchKernelEx(&cfg, gt_norm_kernel, d_gt_hwc, d_x_nchw, npix, C, ch0, zero_render_planes ? ch0 : 0, vec, B,
+                                       (vec && W > 0 && W % 4 == 0) ? d_live_loads : (const unsigned*)nullptr, W, ntx, nt));
     RAC_LAUNCHED();
     return RAC_OK;
 }

@@ -282,6 +282,8 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
         unsigned k[4];
 #pragma unroll
         for (int s = 0; s < 4; ++s) k[s] = inb ? sm.z[s * kTilePix + p] : kKeyEmpty32;
+        // a warp owns one 32-pixel row segment: nothing to list when all of it is background (most of a silhouette bin)
+        if (!__any_sync(0xffffffffu, (k[0] & k[1] & k[2] & k[3]) != kKeyEmpty32)) continue;
         unsigned fresh = 0;
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
@@ -350,10 +352,19 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
     for (int i = 0; i < kPer; ++i) {
         const int p = tid + i * kRasterThreads;
         const int lx = p & (kTileW - 1), ly = p / kTileW;
-        if (lx >= tw || ly >= th) continue;
+        const bool inb = lx < tw && ly < th;
         unsigned k[4];
 #pragma unroll
-        for (int s = 0; s < 4; ++s) k[s] = sm.z[s * kTilePix + p];
+        for (int s = 0; s < 4; ++s) k[s] = inb ? sm.z[s * kTilePix + p] : kKeyEmpty32;
+        if (!__any_sync(0xffffffffu, (k[0] & k[1] & k[2] & k[3]) != kKeyEmpty32)) {     // background row segment
+            if (inb) {
+                const size_t o = img_pix + (size_t)(bc.y_lo + ly) * W + (bc.x_lo + lx);
+                rgba_out[o] = 0u;
+                depth_out[o] = 0.0f;
+            }
+            continue;
+        }
+        if (!inb) continue;
         unsigned sum_r = 0, sum_g = 0, sum_b = 0, sum_a = 0;
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
@@ -423,6 +434,11 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
     const MeshDev& mesh = table[mesh_ids ? mesh_ids[b] : uniform_mesh];
     const int ncta = (mesh.T + kSetupThreads - 1) / kSetupThreads;
     const size_t img_pix = (size_t)b * W * H;
+    // the bin's first descriptor group is requested before anything else: its L2 round trip overlaps the z-buffer
+    // initialisation, the shading-context loads of the last thread and the first barrier
+    const unsigned* dtile = desc + ((size_t)b * tg.nt + tile) * tg.ncta_max;
+    unsigned d_first = 0u;
+    if (tg.binned && tid < ncta) d_first = __ldg(dtile + tid);
     {
         uint4* z4 = reinterpret_cast<uint4*>(sm.z);
         const uint4 e = make_uint4(kKeyEmpty32, kKeyEmpty32, kKeyEmpty32, kKeyEmpty32);
@@ -452,10 +468,9 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
 
     // ---- binned triangles: descriptors of this bin, kRasterThreads at a time ----
     if (tg.binned) {
-        const unsigned* dtile = desc + ((size_t)b * tg.nt + tile) * tg.ncta_max;
         for (int dbase = 0; dbase < ncta; dbase += kRasterThreads) {
             const int j = dbase + tid;
-            const unsigned d = j < ncta ? dtile[j] : 0u;
+            const unsigned d = dbase == 0 ? d_first : (j < ncta ? dtile[j] : 0u);
             const unsigned c = d & 0xFFFFu;
             unsigned incl = c;
 #pragma unroll
