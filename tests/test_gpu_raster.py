@@ -120,6 +120,53 @@ def test_textured_mesh(rac):
     compare(out, ro.render_batch(m, T, K, S), S, S, "textured")
 
 
+def test_config_c4_mixed_meshes_batch_256(rac):
+    """BASELINE configs[3] shape: 256 poses per GPU, 10 distinct meshes of 2k-40k triangles mixed in
+    one batch (per-sample mesh handles, ragged triangle counts), S = 320, C = 6.  A sample of the images is checked
+    against the oracle; the whole batch through size-independent properties."""
+    from rac import mesh as M
+    rng = np.random.default_rng(44)
+    sizes = [2000, 3000, 5000, 8000, 10000, 15000, 20000, 25000, 30000, 40000]
+    pool = [M.bumpy_sphere(level=5 if t <= 20000 else 6, seed=10 + i, decimate_to=t) for i, t in enumerate(sizes)]
+    B, S = 256, 320
+    pick = rng.integers(0, len(pool), B)
+    batch = [pool[i] for i in pick]
+    T, _ = sample_poses(B, seed=44)
+    K = intrinsics(B, S, S)
+    gt = torch.rand((B, S, S, 3), device="cuda")
+    x, depth, rgb = rac.render_concat_device(T, batch, K, S, gt, use_norm_depth=False, want_depth=True, want_rgb=True)
+    assert x.shape == (B, 6, S, S)
+    d = depth.cpu().numpy()
+    cov = (d > 0).reshape(B, -1).mean(1)
+    assert (cov > 0.005).all() and (cov < 0.6).all(), (cov.min(), cov.max())      # 2k of 20k faces kept: ~1 % coverage
+    xr = x[:, 0:3].cpu().numpy()
+    assert np.isfinite(x.cpu().numpy()).all()
+    np.testing.assert_allclose(xr.reshape(B, -1).max(1), 1.0, rtol=0, atol=0)          # max-normalised render (R9)
+    bg = xr[np.repeat((d == 0)[:, None], 3, 1)]                                         # depth = sample 0 only: MSAA edge pixels
+    assert (bg == 0).mean() > 0.97                                                      # may carry colour, the rest is exactly zero
+    xg = x[:, 3:6].cpu().numpy().reshape(B, -1).astype(np.float64)
+    np.testing.assert_allclose(xg.mean(1), 0.0, atol=2e-4)                              # normalize_img: zero mean, unit std
+    np.testing.assert_allclose(xg.std(1), 1.0, atol=2e-4)
+    sample = [0, 17, 101, 200, 255, int(np.argmax([len(m.faces) for m in batch]))]
+    orc = ro.render_batch_mixed([batch[i] for i in sample], T[sample], K[sample], S)
+    compare({"depth": depth[sample], "rgb": rgb[sample], "rgba8": None}, orc, S, S, "C4 sample")
+
+
+def test_config_c3_textured_batch_128(rac):
+    """BASELINE configs[2] shape: 128 poses, textured mesh (512x512 RGB8 noise + checker, R8), S = 320."""
+    from rac import mesh as M
+    m = M.with_texture(M.icosphere(5), size=512, seed=7)
+    B, S = 128, 320
+    T, _ = sample_poses(B, seed=33)
+    K = intrinsics(B, S, S)
+    out = rac.render_batch_device(T, m, K, S, want_rgba8=True)
+    sample = [0, 31, 64, 127]
+    orc = ro.render_batch(m, T[sample], K[sample], S)
+    compare({"depth": out["depth"][sample], "rgb": out["rgb"][sample], "rgba8": out["rgba8"][sample]}, orc, S, S, "C3 sample")
+    q = out["rgba8"].cpu().numpy()
+    assert (q[..., 0].astype(int) != q[..., 2].astype(int)).any(), "the texture must tint the render"
+
+
 def test_edge_cases(rac):
     m = meshes()["box"]
     S = 128
