@@ -227,6 +227,32 @@ def run_ours(args):
         torch.cuda.current_stream().synchronize()
         return x
 
+    ITERS_PER_BATCH = 3      # BASELINE configs[1]: "batch 64, 3 refinement iters"
+
+    def step_e2e_batch(i):
+        """One batch as the reference's loop runs it (train_model.py:224-250): the gt crop is drawn once, then
+        ITERS_PER_BATCH refinement iterations render under the updated pose and re-assemble the input with the SAME
+        gt_imgs object — the shadow prepare_model_input recognises it (torch version counter) and reuses the
+        normalised planes it left on the device instead of uploading and normalising again."""
+        s = dsets[i % NSETS]
+        s["h_gt"][0, 0, 0, 0:1].add_(0)            # a fresh batch: bump the tensor's version so nothing cached matches
+        T_pred = s["h_T_init"].numpy()
+        T_gt = s["h_T_gt"].to(dev, non_blocking=True)
+        pts = s["h_pts"].to(dev, non_blocking=True)
+        for _ in range(ITERS_PER_BATCH):
+            imgs, depths = DL.render_batch_sequential(T_pred, mesh_paths, Ks_cpu, (W, H))      # :240
+            T_dev = torch.tensor(T_pred).to(dev, non_blocking=True)                            # :241
+            x = DL.prepare_model_input(imgs, s["h_gt"], depths, False).to(dev)                 # :243
+            y = s["h_y"].to(dev, non_blocking=True).requires_grad_(True)
+            T_new = RR.calculate_T_CO_pred(y, T_dev, ROT, Ks_cpu)                              # :245
+            l = L.compute_disentangled_ADD_L1_loss(T_gt, T_new, pts)                           # :247 / :280
+            l.backward()
+            h_pose_out.copy_(T_new.detach(), non_blocking=True)                                # :250 (.cpu().numpy())
+            h_loss_out.copy_(l.detach().reshape(1), non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            T_pred = h_pose_out.numpy().copy()
+        return x
+
     def barrier():
         if world > 1:
             dist.barrier()
@@ -261,10 +287,18 @@ def run_ours(args):
     stage_total_ms, _ = timed(step_render_only, args.steps)
     stage_ms = stage_total_ms / args.steps
 
+    from rac import render as _render
+    _render.set_gt_cache(False)      # the per-step end-to-end figure: every step uploads and normalises its own gt crop
     for i in range(max(args.warmup, 3)):
         step_e2e(i)
     e_ms, e_wall_ms = timed(step_e2e, args.steps)
     e_ms = max(e_ms, e_wall_ms)      # e2e includes host work: take the larger of device and wall clocks
+    _render.set_gt_cache(True)       # secondary figure: whole batches of ITERS_PER_BATCH iterations, gt uploaded once per batch
+    nb_batches = max(args.steps // ITERS_PER_BATCH, 4)
+    for i in range(3):
+        step_e2e_batch(i)
+    eb_ms, eb_wall_ms = timed(step_e2e_batch, nb_batches)
+    eb_ms = max(eb_ms, eb_wall_ms)
 
     per_step = ms / args.steps
     value = world * B * args.steps / (ms * 1e-3)
@@ -301,6 +335,11 @@ def run_ours(args):
         "e2e": {"value": world * B * args.steps / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms / args.steps,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 64 + 4,
                 "api": "data_loaders.render_batch_sequential + prepare_model_input + calculate_T_CO_pred + compute_disentangled_ADD_L1_loss + backward"},
+        "e2e_batch": {"value": world * B * ITERS_PER_BATCH * nb_batches / (eb_ms * 1e-3), "unit": UNIT,
+                      "ms_per_batch": eb_ms / nb_batches, "iters_per_batch": ITERS_PER_BATCH, "batches": nb_batches,
+                      "h2d_bytes_per_batch": h2d + (ITERS_PER_BATCH - 1) * (B * 64 + B * 9 * 4), "d2h_bytes_per_batch": ITERS_PER_BATCH * (B * 64 + 4),
+                      "note": "secondary: the reference's loop shape (configs[1]: 3 refinement iterations per drawn batch, same gt_imgs "
+                              "object every iteration) — the gt crop is uploaded and normalised once per batch; `e2e` above pays it every step"},
         "gpu_launches": int(launches), "clocks": clocks,
     }
     if rank == 0:

@@ -393,7 +393,7 @@ int rac_render_concat(const int32_t* h_mesh_ids, const float* d_T_CO, const floa
 int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const float* d_depth, int B, int W, int H,
                        int use_norm_depth, float* d_x_nchw, void* d_stats_ws, size_t ws_bytes, rac_stream_t stream_) {
     cudaStream_t stream = (cudaStream_t)stream_;
-    RAC_REQUIRE(d_init_hwc && d_gt_hwc && d_x_nchw, "rac_assemble_input: null init / gt / x");
+    RAC_REQUIRE(d_init_hwc && d_x_nchw, "rac_assemble_input: null init / x");
     RAC_REQUIRE(B > 0 && W > 0 && H > 0 && B <= 65535, "rac_assemble_input: bad shape B=%d W=%d H=%d", B, W, H);
     RAC_REQUIRE(!use_norm_depth || d_depth, "rac_assemble_input: use_norm_depth needs depth");
     if (!d_stats_ws || ws_bytes < rac_assemble_workspace_bytes(B)) {
@@ -408,7 +408,7 @@ int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const flo
         depth_stats_kernel<<<dim3(chunks, B), 256, 0, stream>>>(stats, d_depth, npix, chunks);
         RAC_LAUNCHED();
     }
-    {
+    if (d_gt_hwc) {      // NULL: the caller fills the gt planes (cached across the refinement iterations of a batch)
         int rc = launch_gt_norm(d_gt_hwc, d_x_nchw, B, npix, use_norm_depth, 0, 0, stream);
         if (rc != RAC_OK) return rc;
     }

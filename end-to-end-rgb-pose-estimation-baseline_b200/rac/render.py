@@ -174,6 +174,45 @@ def _assemble_call(L, init, gt, d, B, W, H, use_norm_depth, x, dev):
     _lib.check(rc)
 
 
+# ---- normalised gt planes kept across the refinement iterations of a batch ----------------------------------
+# The reference normalises and re-uploads the SAME gt crop in every refinement iteration of a batch
+# (train_model.py:234-250: `gt_imgs` is drawn once, prepare_model_input runs inside the `for j` loop).  For torch
+# tensors the (object, storage pointer, in-place version counter) triple identifies unchanged content safely, so the
+# normalised planes of the last few crops stay on the device and later iterations skip the upload and the
+# normalisation.  numpy arrays carry no version counter and are never cached.
+_gt_cache = []          # [(weakref, data_ptr, version, shape, device index, planes (B,3,H,W))], most recent last
+_GT_CACHE_ENTRIES = 2
+_gt_cache_enabled = True
+
+
+def set_gt_cache(enabled):
+    """Switch the cross-iteration gt cache on/off (bench.py's per-step end-to-end figure switches it off: every
+    step must pay its own upload); returns the previous setting."""
+    global _gt_cache_enabled
+    prev = _gt_cache_enabled
+    _gt_cache_enabled = bool(enabled)
+    if not enabled:
+        _gt_cache.clear()
+    return prev
+
+
+def _gt_cache_lookup(t, dev):
+    if not (_gt_cache_enabled and isinstance(t, torch.Tensor)):
+        return None
+    for e in _gt_cache:
+        if e[0]() is t and e[1] == t.data_ptr() and e[2] == t._version and e[3] == tuple(t.shape) and e[4] == dev.index:
+            return e[5]
+    return None
+
+
+def _gt_cache_store(t, dev, planes):
+    if not (_gt_cache_enabled and isinstance(t, torch.Tensor)):
+        return
+    import weakref
+    _gt_cache[:] = [e for e in _gt_cache if e[0]() is not None and e[0]() is not t][-(_GT_CACHE_ENTRIES - 1):]
+    _gt_cache.append((weakref.ref(t), t.data_ptr(), t._version, tuple(t.shape), dev.index, planes.clone()))
+
+
 def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
     """prepare_model_input on renders that already exist (iteration 0): -> x (B,C,H,W) f32 CUDA."""
     L = _lib.lib()
@@ -187,6 +226,11 @@ def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
         assert d.shape == (B, H, W)
     C = 7 if use_norm_depth else 6
     x = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
+    cached = _gt_cache_lookup(gt_hwc, dev)
+    if cached is not None:
+        x[:, C - 3:].copy_(cached)
+        _assemble_call(L, init, None, d, B, W, H, use_norm_depth, x, dev)
+        return x
     if _overlappable(gt_hwc) and B >= 2 * _GT_CHUNKS:
         main = torch.cuda.current_stream(dev)
         cs = _copy_stream(dev)
@@ -210,9 +254,11 @@ def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
         done = torch.cuda.Event()
         done.record(main)
         ring["done"][slot] = done
+        _gt_cache_store(gt_hwc, dev, x[:, C - 3:])
         return x
     gt = torch.as_tensor(gt_hwc).to(device=dev, dtype=torch.float32).contiguous()
     _assemble_call(L, init, gt, d, B, W, H, use_norm_depth, x, dev)
+    _gt_cache_store(gt_hwc, dev, x[:, C - 3:])
     return x
 
 

@@ -127,6 +127,8 @@ RAC_API int rac_render_concat(const int32_t* h_mesh_ids, const float* d_T_CO, co
 /* ref: data_loaders.py:158-177 (prepare_model_input) alone, for renders that already
  * exist (iteration 0 uses the dataset's init render, train_model.py:236-243).
  * d_init_hwc (B,H,W,3) f32, d_gt_hwc (B,H,W,3) f32, d_depth (B,H,W) f32 (nullable unless use_norm_depth).
+ * d_gt_hwc == NULL: the gt planes of x are left untouched (the caller keeps the normalised crop of a batch across
+ * its refinement iterations, train_model.py:234-250, and copies it in itself).
  * d_stats_ws: device scratch of rac_assemble_workspace_bytes(B) bytes. */
 RAC_API size_t rac_assemble_workspace_bytes(int B);
 RAC_API int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const float* d_depth,

@@ -256,6 +256,35 @@ def test_assemble_input_pinned_gt_overlapped_upload(rac, B, use_depth):
         np.testing.assert_allclose(over.cpu().numpy(), ref, rtol=1e-5, atol=2e-5)
 
 
+def test_gt_cache_across_refinement_iterations(rac):
+    """The same torch gt tensor passed again (the reference's `for j` loop, train_model.py:234-250) reuses the
+    normalised planes left on the device; an in-place change or a different tensor does not."""
+    from rac import render as R
+    rng = np.random.default_rng(21)
+    B, H, W = 8, 48, 64
+    mk = lambda: torch.tensor(rng.uniform(0, 1, (B, H, W, 3)).astype(np.float32), device="cuda")
+    init1, init2 = mk(), mk()
+    gt = torch.tensor((rng.integers(0, 256, (B, H, W, 3)) / 255.0).astype(np.float32)).pin_memory()
+    prev = R.set_gt_cache(True)
+    try:
+        x1 = rac.assemble_input_device(init1, gt, None, False)
+        assert R._gt_cache_lookup(gt, x1.device) is not None
+        x2 = rac.assemble_input_device(init2, gt, None, False)            # hit: gt planes come from the cache
+        ref2 = assemble_ref.prepare_model_input(init2.cpu().numpy(), gt.numpy().astype(np.float64), None, False).numpy()
+        assert torch.equal(x1[:, 3:], x2[:, 3:])
+        np.testing.assert_allclose(x2.cpu().numpy(), ref2, rtol=1e-5, atol=2e-5)
+        gt.mul_(0.5)                                                      # in-place change -> version bump -> miss
+        assert R._gt_cache_lookup(gt, x1.device) is None
+        x3 = rac.assemble_input_device(init2, gt, None, False)
+        ref3 = assemble_ref.prepare_model_input(init2.cpu().numpy(), gt.numpy().astype(np.float64), None, False).numpy()
+        np.testing.assert_allclose(x3.cpu().numpy(), ref3, rtol=1e-5, atol=2e-5)
+        assert R._gt_cache_lookup(gt.numpy(), x1.device) is None          # numpy arrays are never cached
+        R.set_gt_cache(False)
+        assert R._gt_cache_lookup(gt, x1.device) is None
+    finally:
+        R.set_gt_cache(prev)
+
+
 def test_reference_api_modules(rac, tmp_path):
     """The drop-in modules: renderer.render_scene, data_loaders.render_batch / prepare_model_input."""
     import data_loaders
