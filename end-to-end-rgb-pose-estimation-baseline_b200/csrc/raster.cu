@@ -290,7 +290,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
     }
     if (!(skip & 2)) {
         dim3 grid(tg.ncta_max, B);
-        setup_kernel<<<grid, kSetupThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
+        setup_kernel<<<grid, kSetupCtaThreads, 0, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S.znear,
                                                          ws.stats, ws.large_cnt, ws.large_tri, ws.recs, ws.desc, ws.refs,
                                                          ws.ctl, ws.loads, ws.buckets);
         RAC_LAUNCHED();
