@@ -81,9 +81,12 @@ __device__ __forceinline__ void load_bucket_prefix(const WorkCtl* __restrict__ c
 // with plain stores — no global atomics, nothing to zero beforehand.  The others ("large": rare for ModelNet-scale
 // meshes, the common case for 12-triangle boxes) are compacted, in triangle order, into the CTA's slice of the image's
 // large list: large_tri[b][cta * 256 + k], k < large_cnt[b][cta] — deterministic, unlike an atomic append.
-constexpr int kSetupCtaThreads = 128;
+#ifndef RAC_SETUP_CTA_THREADS
+#define RAC_SETUP_CTA_THREADS 128
+#endif
+constexpr int kSetupCtaThreads = RAC_SETUP_CTA_THREADS;
 constexpr int kSetupPer = kSetupThreads / kSetupCtaThreads;     // triangles per thread
-static_assert(kSetupPer == 2, "setup_body is written for two triangles per thread");
+static_assert(kSetupPer * kSetupCtaThreads == kSetupThreads && kSetupCtaThreads >= 64, "refs copy-out needs >= 64 threads");
 
 __device__ __forceinline__ void
 setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, int uniform_mesh,
@@ -165,7 +168,7 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         large[k] = keep[k] && !small[k];
     }
     __syncthreads();   // s_cnt zeroed
-    unsigned slot[kSetupPer] = {0u, 0u};     // position within each of the (up to 4) bins, 8 bits each (count <= 256 -> pos <= 255)
+    unsigned slot[kSetupPer] = {};           // position within each of the (up to 4) bins, 8 bits each (count <= 256 -> pos <= 255)
 #pragma unroll
     for (int k = 0; k < kSetupPer; ++k) {
         if (small[k]) {
