@@ -88,27 +88,32 @@ finalize_live_kernel(FinArgs A, TileGrid tg, int H, const unsigned* __restrict__
         const unsigned e = bucket_entry(s_prefix, buckets, bucket_cap, r);
         const int b = (int)(e / (unsigned)tg.nt), tile = (int)(e % (unsigned)tg.nt);
         const int x = (tile % tg.ntx) * kTileW + lx, y = (tile / tg.ntx) * kTileH + ly;
-        const ImgStats st = load_stats_cg(A.stats + b);
-        const NormConsts n = load_norm(st, A.use_norm_depth != 0);
-        __syncthreads();              // previous bin's lookups are done
-        for (int q = threadIdx.x; q < 256; q += kFinThreads) s_lut[q] = norm_col1((unsigned)q, n);
-        __syncthreads();
-        if (y >= H || x >= W) continue;
+        // the bin's pixels are requested first: their L2 round trip overlaps the per-image statistics load and the
+        // construction of the lookup table (two barriers) instead of following them
+        const bool inside = y < H && x < W;
         const size_t pi = (size_t)b * npix + (size_t)y * W + x;
         const int nv = min(4, W - x);
         unsigned c[4] = {0u, 0u, 0u, 0u};
         float d[4] = {0.f, 0.f, 0.f, 0.f};
         const bool want_d = A.depth_out || (A.x_nchw && A.use_norm_depth);
-        if (A.vec) {
-            const uint4 cv = __ldcg(reinterpret_cast<const uint4*>(A.rgba + pi));
-            c[0] = cv.x; c[1] = cv.y; c[2] = cv.z; c[3] = cv.w;
-            if (want_d) {
-                const float4 dv = __ldcg(reinterpret_cast<const float4*>(A.depth + pi));
-                d[0] = dv.x; d[1] = dv.y; d[2] = dv.z; d[3] = dv.w;
+        if (inside) {
+            if (A.vec) {
+                const uint4 cv = __ldcg(reinterpret_cast<const uint4*>(A.rgba + pi));
+                c[0] = cv.x; c[1] = cv.y; c[2] = cv.z; c[3] = cv.w;
+                if (want_d) {
+                    const float4 dv = __ldcg(reinterpret_cast<const float4*>(A.depth + pi));
+                    d[0] = dv.x; d[1] = dv.y; d[2] = dv.z; d[3] = dv.w;
+                }
+            } else {
+                for (int i = 0; i < nv; ++i) { c[i] = __ldcg(A.rgba + pi + i); if (want_d) d[i] = __ldcg(A.depth + pi + i); }
             }
-        } else {
-            for (int i = 0; i < nv; ++i) { c[i] = __ldcg(A.rgba + pi + i); if (want_d) d[i] = __ldcg(A.depth + pi + i); }
         }
+        const ImgStats st = load_stats_cg(A.stats + b);
+        const NormConsts n = load_norm(st, A.use_norm_depth != 0);
+        __syncthreads();              // previous bin's lookups are done
+        for (int q = threadIdx.x; q < 256; q += kFinThreads) s_lut[q] = norm_col1((unsigned)q, n);
+        __syncthreads();
+        if (!inside) continue;
         float rr[4], gg[4], bb[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
