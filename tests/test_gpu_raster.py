@@ -167,6 +167,19 @@ def test_config_c3_textured_batch_128(rac):
     assert (q[..., 0].astype(int) != q[..., 2].astype(int)).any(), "the texture must tint the render"
 
 
+def test_unbinned_large_image(rac):
+    """More than 2048 bins per image (here 2048x1536 = 6144 bins): setup skips binning and every survivor goes to the
+    per-image large list (int64 edge functions, every bin scans the list)."""
+    ms = meshes()
+    batch = [ms["box"], ms["ico3"]]
+    W, H = 2048, 1536
+    T, _ = sample_poses(2, seed=12)
+    K = intrinsics(2, W, H)
+    out = rac.render_batch_device(T, batch, K, (W, H), want_rgba8=True)
+    compare(out, ro.render_batch_mixed(batch, T, K, (W, H)), W, H, "unbinned")
+    assert (out["depth"] > 0).float().mean() > 0.02
+
+
 def test_edge_cases(rac):
     m = meshes()["box"]
     S = 128
