@@ -9,6 +9,8 @@ from ._lib import RAC_POSE_SAVED_FLOATS, RAC_ROT
 
 
 def _cu(t, dtype=torch.float32):
+    if t.is_cuda and t.dtype == dtype and t.is_contiguous():     # the common case: nothing to stage or convert
+        return t.detach()
     dev = _lib.require_cuda()
     return t.detach().to(device=dev, dtype=dtype).contiguous()
 

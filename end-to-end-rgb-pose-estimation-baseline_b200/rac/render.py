@@ -65,10 +65,28 @@ def _resolve_meshes(meshes, B):
     return (ctypes.c_int * B)(*handles), maxT
 
 
+_k_cache = []          # [(weakref to the host tensor, data_ptr, version, device index, device copy)]
+
+
+def _intrinsics_on_device(K, dev):
+    """The drivers pass the same CPU `cam_mats` tensor in every call (train_model.py:240, Q5): its device copy is kept,
+    keyed by the tensor object, its storage pointer and its in-place version counter."""
+    if isinstance(K, torch.Tensor) and not K.is_cuda:
+        for e in _k_cache:
+            if e[0]() is K and e[1] == K.data_ptr() and e[2] == K._version and e[3] == dev.index:
+                return e[4]
+        Kt = K.to(device=dev, dtype=torch.float32).contiguous()
+        import weakref
+        _k_cache[:] = [e for e in _k_cache if e[0]() is not None and e[0]() is not K][-3:]
+        _k_cache.append((weakref.ref(K), K.data_ptr(), K._version, dev.index, Kt))
+        return Kt
+    return torch.as_tensor(K).to(device=dev, dtype=torch.float32).contiguous()
+
+
 def _prep(T_CO, K, meshes):
     dev = _lib.require_cuda()
     T = torch.as_tensor(T_CO).to(device=dev, dtype=torch.float32).contiguous()
-    Kt = torch.as_tensor(K).to(device=dev, dtype=torch.float32).contiguous()
+    Kt = _intrinsics_on_device(K, dev)
     B = T.shape[0]
     assert T.shape == (B, 4, 4)
     assert Kt.shape == (B, 3, 3)
