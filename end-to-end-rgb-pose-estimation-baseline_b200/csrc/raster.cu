@@ -310,7 +310,8 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         const int grid = (int)min((long long)grid_max, (long long)B * tg.nt);
         raster_kernel<<<grid, kRasterThreads, kRasterSmemBytes, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,
                                                                           ws.stats, ws.large_cnt, ws.large_tri, ws.recs, ws.desc, ws.refs,
-                                                                          ws.ctl, ws.buckets, (size_t)B * tg.nt, ws.rgba, ws.depth, ws.scratch_col,
+                                                                          ws.ctl, ws.buckets, (size_t)B * tg.nt, ws.rgba,
+                                                                          (fin.depth_out || (fin.x_nchw && fin.use_norm_depth)) ? ws.depth : (float*)nullptr, ws.scratch_col,
                                                                           (fin.x_nchw && fin.use_norm_depth) ? 1 : 0);
         RAC_LAUNCHED();
     }

@@ -243,8 +243,9 @@ __device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, un
     }
     __syncthreads();
     RAC_PHASE(4);
+    // (no barrier after the reset: consecutive batches alternate between two counters, and this one is next bumped
+    // two batches — several barriers — from here)
     if (tid == 0) *med_count = 0;
-    __syncthreads();
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -360,7 +361,7 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
             if (inb) {
                 const size_t o = img_pix + (size_t)(bc.y_lo + ly) * W + (bc.x_lo + lx);
                 rgba_out[o] = 0u;
-                depth_out[o] = 0.0f;
+                if (depth_out) depth_out[o] = 0.0f;
             }
             continue;
         }
@@ -385,13 +386,15 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
         const unsigned r8 = (sum_r + 2u) >> 2, g8 = (sum_g + 2u) >> 2, b8 = (sum_b + 2u) >> 2, a8 = (sum_a + 2u) >> 2;
         const size_t o = img_pix + (size_t)(bc.y_lo + ly) * W + (bc.x_lo + lx);
         rgba_out[o] = r8 | (g8 << 8) | (b8 << 16) | (a8 << 24);
-        float depth = 0.0f;
-        if (k[0] != kKeyEmpty32) depth = depth_readback(k[0] >> 8, S);
-        depth_out[o] = depth;
         acc.qmax = max(acc.qmax, max(r8, max(g8, b8)));
-        if (need_dstats) {      // normalize_depth statistics: only when the caller asked for the normalised depth plane
-            acc.dmax = fmaxf(acc.dmax, depth);
-            if (depth > 0.01f) { acc.dcount++; acc.dsum += (double)depth; acc.dsumsq += (double)depth * (double)depth; }
+        if (depth_out) {        // kernel-uniform: nobody reads the metric depth of a 6-channel concat without depth output
+            float depth = 0.0f;
+            if (k[0] != kKeyEmpty32) depth = depth_readback(k[0] >> 8, S);
+            depth_out[o] = depth;
+            if (need_dstats) {  // normalize_depth statistics: only when the caller asked for the normalised depth plane
+                acc.dmax = fmaxf(acc.dmax, depth);
+                if (depth > 0.01f) { acc.dcount++; acc.dsum += (double)depth; acc.dsumsq += (double)depth * (double)depth; }
+            }
         }
     }
 }
@@ -406,7 +409,7 @@ __device__ __noinline__ void commit_bin(RasterSmem& sm, int* q_count, const BinC
 // ---------------------------------------------------------------------------------------------
 // one bin, start to finish
 // ---------------------------------------------------------------------------------------------
-// s_ctl: [0] resolve item count, [1] medium-triangle count (both zero on entry and on exit);
+// s_ctl: [0] resolve item count, [1], [2] medium-triangle counts of alternating batches (all zero on entry and on exit);
 // s_scan: [4 * kRasterThreads + 8] descriptor counts / scan / offsets / large counts / warp sums.
 __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned* s_scan, ShadeCtx* s_sc, unsigned* __restrict__ scratch_col,
                                             const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids,
@@ -420,6 +423,7 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
                                             const unsigned* __restrict__ buckets, size_t bucket_cap, unsigned* s_next,
                                             int need_dstats RAC_PHASE_ARGS) {
     int* q_count = s_ctl, *med_count = s_ctl + 1;
+    int batch_no = 0;          // CTA-uniform: selects the medium-triangle counter of the batch
     unsigned* s_dcnt = s_scan;                      // [kRasterThreads] descriptor counts (large pass: per-CTA counts)
     unsigned* s_dscan = s_scan + kRasterThreads;    // [kRasterThreads] exclusive scan
     unsigned* s_doff = s_scan + 2 * kRasterThreads; // [kRasterThreads] offset into the ref region
@@ -460,7 +464,8 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
                 commit_bin(sm, q_count, bc, scratch_col, s_sc, S RAC_PHASE_PASS);
                 nslots = 0;
             }
-            process_batch<LARGE>(sm, med_count, s_wsum, bc, sm.queue + qb, n, (unsigned)nslots + 1u RAC_PHASE_PASS);
+            process_batch<LARGE>(sm, med_count + (batch_no & 1), s_wsum, bc, sm.queue + qb, n, (unsigned)nslots + 1u RAC_PHASE_PASS);
+            ++batch_no;
             nslots += n;
         }
     };
@@ -617,7 +622,7 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
               int need_dstats) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RasterSmem& sm = *reinterpret_cast<RasterSmem*>(smem_raw);
-    __shared__ int s_ctl[2];
+    __shared__ int s_ctl[3];
     __shared__ unsigned s_next[2];     // ticket and work-list entry of the CTA's next bin
     __shared__ unsigned s_scan[3 * kRasterThreads + kRasterWarpsN];
     __shared__ ShadeCtx s_sc;
@@ -637,7 +642,7 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
     }
 #endif
     // The first ticket is the CTA's own index (no atomic before the first bin); later tickets come from the counter.
-    if (threadIdx.x == 0) { s_ctl[0] = 0; s_ctl[1] = 0; }
+    if (threadIdx.x == 0) { s_ctl[0] = 0; s_ctl[1] = 0; s_ctl[2] = 0; }
     __syncthreads();
     const unsigned n_work = s_prefix[kBuckets];
     unsigned r = blockIdx.x;
