@@ -469,7 +469,9 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
             nslots += n;
         }
     };
-    __syncthreads();
+    // (binned images: the descriptor scan below starts with barriers of its own, well before anything reads the
+    // z-buffer, the control words or the shading context initialised above)
+    if (!tg.binned) __syncthreads();
 
     // ---- binned triangles: descriptors of this bin, kRasterThreads at a time ----
     if (tg.binned) {
