@@ -643,11 +643,13 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
         atomicAdd(&g_tl[9], t - g_tl[15]);
     }
 #endif
-    // The first ticket is the CTA's own index (no atomic before the first bin); later tickets come from the counter.
-    if (threadIdx.x == 0) { s_ctl[0] = 0; s_ctl[1] = 0; s_ctl[2] = 0; }
+    // Every ticket, the first included, comes from the counter: a CTA that becomes resident late (the step graph runs
+    // the pose / loss kernels and the gt kernel next to this one) must not own one of the heaviest bins — handing the
+    // first tickets out by CTA index was measured 2 % slower for exactly that reason.
+    if (threadIdx.x == 0) { s_ctl[0] = 0; s_ctl[1] = 0; s_ctl[2] = 0; s_next[0] = atomicAdd(&ctl->next, 1u); }
     __syncthreads();
     const unsigned n_work = s_prefix[kBuckets];
-    unsigned r = blockIdx.x;
+    unsigned r = s_next[0];
     unsigned e = r < n_work ? bucket_entry(s_prefix, buckets, bucket_cap, r) : 0u;   // image * nt + bin, heaviest class first
     while (r < n_work) {
 #ifdef RAC_PHASE_TIMING
@@ -662,7 +664,7 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
 #endif
 #endif
         unsigned r_next = 0;
-        if (threadIdx.x == 0) r_next = gridDim.x + atomicAdd(&ctl->next, 1u);   // parked in s_next before the resolve
+        if (threadIdx.x == 0) r_next = atomicAdd(&ctl->next, 1u);   // parked in s_next before the resolve
         RAC_PHASE(0);
         raster_tile(sm, s_ctl, s_scan, &s_sc, my_scratch, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_cnt,
                     large_tri, recs, desc, refs, rgba_out, depth_out, (int)(e / (unsigned)tg.nt), (int)(e % (unsigned)tg.nt),
