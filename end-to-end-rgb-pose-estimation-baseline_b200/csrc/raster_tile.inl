@@ -2,7 +2,7 @@
 // Included by raster.cu (inside namespace rac).
 //
 //   gather    the bin's descriptors (one per setup CTA) -> u8 ref regions -> triangle ids in a shared queue;
-//   coverage  batches of <= 254 triangles, thread = triangle: triangles with <= 16 bbox pixels are staged (int32 edge
+//   coverage  batches of <= 254 triangles, thread = triangle: triangles with <= 20 bbox pixels are staged (int32 edge
 //             equations relative to the clipped bbox) and their (triangle, pixel) items flattened over the warp, 32
 //             per step; larger ones are walked by a whole warp each.  Exact edge functions, top-left rule, 4 samples;
 //   depth     24-bit depth and the triangle's batch-local id form one 32-bit key (d24 << 8 | id): the z-test is ONE
@@ -39,7 +39,10 @@ constexpr int kRasterThreads = 256;
 constexpr int kRasterWarpsN = kRasterThreads / 32;
 constexpr int kQueueCap = 1024;       // triangle ids gathered per round
 constexpr int kBatch = 254;           // triangles per coverage batch = local ids 1..254 (0 = committed, 0xFF = the empty key)
-constexpr int kSmallPix = 16;         // bbox∩bin pixels handled as flattened items; larger -> one warp per triangle
+#ifndef RAC_SMALL_PIX
+#define RAC_SMALL_PIX 20
+#endif
+constexpr int kSmallPix = RAC_SMALL_PIX;   // bbox∩bin pixels handled as flattened items; larger -> one warp per triangle
 constexpr int kTilePix = kTileW * kTileH;
 constexpr int kTriStride = 20;        // words per staged triangle (16 used; 80 B keeps LDS.128 aligned and conflict-free)
 constexpr unsigned kKeyEmpty32 = 0xFFFFFFFFu;
@@ -51,7 +54,7 @@ struct __align__(16) RasterSmem {
     int queue[kQueueCap];                          //  4 KB gathered triangle ids
     int medq[kRasterThreads];                      //  1 KB batch-local ids of medium triangles
     int tri[kRasterThreads * kTriStride];          // 20 KB staged triangles by local id - 1: edge equations (coverage) + plane, normal (shading)
-    unsigned short items[kRasterThreads * kSmallPix];       // 8 KB flattened (triangle, pixel) items of the batch; resolve: (pixel, sample) items
+    unsigned short items[kRasterThreads * kSmallPix];       // 10 KB flattened (triangle, pixel) items of the batch; resolve: (pixel, sample) items
     unsigned slots[kBatch + 2];                    //  1 KB local id - 1 -> triangle id
     unsigned cols[4 * kTilePix];                   //  8 KB resolve: colour of each pixel's representative samples
 };
@@ -157,7 +160,7 @@ __device__ __forceinline__ void process_batch(RasterSmem& sm, int* med_count, un
             int4* slot = reinterpret_cast<int4*>(sm.tri + (local - 1u) * kTriStride);
             slot[3] = make_int4(__float_as_int(g.gy), __float_as_int(g.iz0), g.X0, g.Y0);
             slot[4] = make_int4(q2.y, q2.z, q2.w, __float_as_int(g.gx));
-            if (!LARGE && w * h <= kSmallPix) {
+            if (!LARGE && w * h <= kSmallPix && w <= 16 && h <= 16) {      // (dx, dy are 4-bit fields of an item)
                 nit = w * h;
                 const int dx0 = g.X1 - g.X0, dy0 = g.Y1 - g.Y0;
                 const int dx1 = g.X2 - g.X1, dy1 = g.Y2 - g.Y1;
