@@ -632,6 +632,8 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
     __shared__ unsigned s_scan[3 * kRasterThreads + kRasterWarpsN];
     __shared__ ShadeCtx s_sc;
     __shared__ unsigned s_prefix[kBuckets + 1];
+    unsigned first_ticket = 0;                       // requested before the bucket counts: the two L2 round trips overlap
+    if (threadIdx.x == 0) first_ticket = atomicAdd(&ctl->next, 1u);
     load_bucket_prefix(ctl, s_prefix);               // final: written by setup_kernel (previous launch)
     unsigned* my_scratch = scratch_col + (size_t)blockIdx.x * kScratchPerCta;
 #ifdef RAC_PHASE_TIMING
@@ -649,7 +651,7 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
     // Every ticket, the first included, comes from the counter: a CTA that becomes resident late (the step graph runs
     // the pose / loss kernels and the gt kernel next to this one) must not own one of the heaviest bins — handing the
     // first tickets out by CTA index was measured 2 % slower for exactly that reason.
-    if (threadIdx.x == 0) { s_ctl[0] = 0; s_ctl[1] = 0; s_ctl[2] = 0; s_next[0] = atomicAdd(&ctl->next, 1u); }
+    if (threadIdx.x == 0) { s_ctl[0] = 0; s_ctl[1] = 0; s_ctl[2] = 0; s_next[0] = first_ticket; }
     __syncthreads();
     const unsigned n_work = s_prefix[kBuckets];
     unsigned r = s_next[0];
