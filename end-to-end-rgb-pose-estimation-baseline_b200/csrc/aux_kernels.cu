@@ -1,6 +1,7 @@
 // aux_kernels.cu — the two "next" rows of SURVEY.md §8(f) that sit either side of the hot path:
 //   N3  batched pose sampling: se3_helpers.get_T_CO_init_and_gt (se3_helpers.py:76-88) for B samples in one launch;
-//   N4  silhouette ring + overlay blend: visualization.create_silhouette / blend_imgs (visualization.py:19-41).
+//   N4  silhouette ring + overlay blend: visualization.create_silhouette / blend_imgs (visualization.py:19-41);
+//   and the 8-bit form of the gt crop (image_dataloaders.py:79-83 + data_loaders.py:79-82 from the raw bytes).
 // Both are tiny streaming kernels (launch-latency bound for N3, HBM bound for N4); no tensor cores.
 #include "rac_common.cuh"
 #include <math.h>
@@ -139,6 +140,98 @@ blend_kernel(const float* __restrict__ a, const float* __restrict__ b, float alp
     out[i] = (float)((double)q / 255.0);
 }
 
+// ---------------------------------------------------------------------------------------------
+// 8-bit gt crops: normalize_img(real.png / 255.0) from the raw bytes
+// ---------------------------------------------------------------------------------------------
+// image_dataloaders.py:79-83 divides the crop by 255 on the host (f64) and data_loaders.py:79-82 normalises it; both
+// are functions of the 8-bit codes alone, so the crop crosses PCIe as bytes (3 B/px instead of 12) and the division
+// moves here.  Sum and sum of squares of the codes are exact integers (order-independent atomics: deterministic);
+// mean and population std follow in f64, and every output value is one of 256 per image: a table of
+// (float)((q / 255.0 - mean) / std), each entry evaluated in f64 like numpy and rounded once, so the planes match
+// the reference's f64 -> f32 cast bit for bit (no zero-std guard: a constant crop gives nan, as in the reference).
+constexpr int kGtU8Threads = 256;      // = the 256 table entries, one per thread
+
+__global__ void __launch_bounds__(kGtU8Threads)
+gt_u8_stats_kernel(const unsigned char* __restrict__ gt, size_t nbytes_img, unsigned long long* __restrict__ stats) {
+    const int b = blockIdx.y;
+    const unsigned char* g = gt + (size_t)b * nbytes_img;
+    const size_t nslice = (nbytes_img + gridDim.x - 1) / gridDim.x;
+    size_t i0 = (size_t)blockIdx.x * nslice, i1 = min(nbytes_img, i0 + nslice);
+    unsigned long long s = 0, ss = 0;
+    if (i0 < i1) {
+        // head up to a 16-B boundary, 16-B body, tail
+        size_t a0 = min(i1, (i0 + ((16 - ((uintptr_t)(g + i0) & 15)) & 15)));
+        for (size_t i = i0 + threadIdx.x; i < a0; i += kGtU8Threads) { const unsigned v = g[i]; s += v; ss += v * v; }
+        const size_t nvec = (i1 - a0) / 16;
+        const uint4* g4 = reinterpret_cast<const uint4*>(g + a0);
+        for (size_t q = threadIdx.x; q < nvec; q += kGtU8Threads) {
+            const uint4 w = __ldcs(g4 + q);
+            const unsigned ws[4] = {w.x, w.y, w.z, w.w};
+            unsigned ls = 0, lss = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                ls = __dp4a(ws[k], 0x01010101u, ls);      // sum of the four bytes
+                lss = __dp4a(ws[k], ws[k], lss);          // sum of their squares (unsigned x unsigned)
+            }
+            s += ls; ss += lss;
+        }
+        for (size_t i = a0 + nvec * 16 + threadIdx.x; i < i1; i += kGtU8Threads) { const unsigned v = g[i]; s += v; ss += v * v; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { s += __shfl_xor_sync(0xffffffffu, s, o); ss += __shfl_xor_sync(0xffffffffu, ss, o); }
+    __shared__ unsigned long long sh[2][kGtU8Threads / 32];
+    if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = s; sh[1][threadIdx.x >> 5] = ss; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned long long a = 0, c = 0;
+        for (int w = 0; w < kGtU8Threads / 32; ++w) { a += sh[0][w]; c += sh[1][w]; }
+        atomicAdd(stats + 2 * b, a);
+        atomicAdd(stats + 2 * b + 1, c);
+    }
+}
+
+__global__ void __launch_bounds__(kGtU8Threads)
+gt_u8_apply_kernel(const unsigned char* __restrict__ gt, int npix, const unsigned long long* __restrict__ stats,
+                   float* __restrict__ x_nchw, int C, int vec) {
+    const int b = blockIdx.y;
+    __shared__ float lut[256];
+    {
+        const unsigned long long S = stats[2 * b], SS = stats[2 * b + 1];
+        const double n = 3.0 * (double)npix;
+        const double mean = (double)S / (255.0 * n);
+        // n SS - S^2 is an exact integer (< 2^63 up to 2.9 M values per image), rounded once on conversion
+        const unsigned long long nn = 3ull * (unsigned long long)npix;
+        double var;
+        if ((double)nn * 65025.0 * (double)nn < 9.0e18) var = (double)(nn * SS - S * S) / (65025.0 * n * n);
+        else var = (double)SS / (65025.0 * n) - mean * mean;
+        const double sd = sqrt(var > 0.0 ? var : 0.0);
+        lut[threadIdx.x] = (float)(((double)threadIdx.x / 255.0 - mean) / sd);
+    }
+    __syncthreads();
+    const unsigned char* g = gt + 3 * (size_t)b * npix;
+    float* xb = x_nchw + ((size_t)b * C + (C - 3)) * (size_t)npix;
+    if (vec) {      // 4 pixels = 12 bytes = three aligned words per step, one float4 store per plane
+        const unsigned* g32 = reinterpret_cast<const unsigned*>(g);
+        const int nq = npix >> 2;
+        for (int q = blockIdx.x * kGtU8Threads + threadIdx.x; q < nq; q += gridDim.x * kGtU8Threads) {
+            const unsigned w0 = __ldcs(g32 + 3 * (size_t)q), w1 = __ldcs(g32 + 3 * (size_t)q + 1), w2 = __ldcs(g32 + 3 * (size_t)q + 2);
+            // bytes: r0 g0 b0 r1 | g1 b1 r2 g2 | b2 r3 g3 b3
+            __stcs(reinterpret_cast<float4*>(xb) + q,
+                   make_float4(lut[w0 & 255u], lut[w0 >> 24], lut[(w1 >> 16) & 255u], lut[(w2 >> 8) & 255u]));
+            __stcs(reinterpret_cast<float4*>(xb + npix) + q,
+                   make_float4(lut[(w0 >> 8) & 255u], lut[w1 & 255u], lut[w1 >> 24], lut[(w2 >> 16) & 255u]));
+            __stcs(reinterpret_cast<float4*>(xb + 2 * (size_t)npix) + q,
+                   make_float4(lut[(w0 >> 16) & 255u], lut[(w1 >> 8) & 255u], lut[w2 & 255u], lut[w2 >> 24]));
+        }
+    } else {
+        for (int p = blockIdx.x * kGtU8Threads + threadIdx.x; p < npix; p += gridDim.x * kGtU8Threads) {
+            xb[p] = lut[g[3 * (size_t)p]];
+            xb[(size_t)npix + p] = lut[g[3 * (size_t)p + 1]];
+            xb[2 * (size_t)npix + p] = lut[g[3 * (size_t)p + 2]];
+        }
+    }
+}
+
 }  // namespace rac
 
 using namespace rac;
@@ -173,6 +266,36 @@ int rac_blend(const float* d_im1, const float* d_im2, float alpha, int quantized
     RAC_REQUIRE(n > 0 && n < ((size_t)1 << 40), "rac_blend: bad element count");
     RAC_REQUIRE(alpha >= 0.0f && alpha <= 1.0f, "rac_blend: alpha=%f outside [0,1]", (double)alpha);
     blend_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream_>>>(d_im1, d_im2, alpha, quantized_inputs, n, d_out);
+    RAC_LAUNCHED();
+    return RAC_OK;
+}
+
+size_t rac_gt_u8_workspace_bytes(int B) { return B > 0 ? 16 * (size_t)B : 0; }
+
+int rac_gt_norm_u8(const unsigned char* d_gt_hwc_u8, int B, int W, int H, int use_norm_depth, float* d_x_nchw,
+                   void* d_stats_ws, size_t ws_bytes, rac_stream_t stream_) {
+    RAC_REQUIRE(d_gt_hwc_u8 && d_x_nchw && d_stats_ws, "rac_gt_norm_u8: null pointer");
+    RAC_REQUIRE(B > 0 && W > 0 && H > 0 && (long long)W * H <= (1ll << 28), "rac_gt_norm_u8: bad shape B=%d W=%d H=%d", B, W, H);
+    RAC_REQUIRE(ws_bytes >= rac_gt_u8_workspace_bytes(B), "rac_gt_norm_u8: workspace too small (%zu < %zu)", ws_bytes,
+                rac_gt_u8_workspace_bytes(B));
+    RAC_REQUIRE(((uintptr_t)d_stats_ws & 7u) == 0, "rac_gt_norm_u8: workspace must be 8-byte aligned");
+    RAC_REQUIRE(B <= 65535, "rac_gt_norm_u8: B=%d exceeds 65535 images per call", B);
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int npix = W * H;
+    const int C = use_norm_depth ? 7 : 6;
+    RAC_CUDA_CHECK(cudaMemsetAsync(d_stats_ws, 0, 16 * (size_t)B, stream));
+    // slices: enough CTAs to fill the GPU at small B, at least 16 KB of bytes each
+    const size_t nbytes_img = 3 * (size_t)npix;
+    int slices = (int)max((size_t)1, min((size_t)(1184 / B + 1), nbytes_img / 16384 + 1));
+    RAC_MAX_CARVEOUT_ONCE(gt_u8_stats_kernel);
+    gt_u8_stats_kernel<<<dim3(slices, B), kGtU8Threads, 0, stream>>>(d_gt_hwc_u8, nbytes_img, (unsigned long long*)d_stats_ws);
+    RAC_LAUNCHED();
+    const int vec = (npix % 4 == 0 && ((uintptr_t)d_gt_hwc_u8 & 3u) == 0 && ((uintptr_t)d_x_nchw & 15u) == 0) ? 1 : 0;
+    const int units = vec ? npix / 4 : npix;
+    int aslices = max(1, min(1184 / B + 1, (units + kGtU8Threads * 4 - 1) / (kGtU8Threads * 4)));
+    RAC_MAX_CARVEOUT_ONCE(gt_u8_apply_kernel);
+    gt_u8_apply_kernel<<<dim3(aslices, B), kGtU8Threads, 0, stream>>>(d_gt_hwc_u8, npix, (const unsigned long long*)d_stats_ws,
+                                                                      d_x_nchw, C, vec);
     RAC_LAUNCHED();
     return RAC_OK;
 }

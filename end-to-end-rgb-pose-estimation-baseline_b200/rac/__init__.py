@@ -9,9 +9,9 @@ rac.mesh (load / procedural / device cache), rac.ops (autograd functions), and t
 from . import _lib, mesh, ops
 from ._lib import RacError, launch_count, lib
 from .aux import blend_device, sample_poses_device, silhouette_device
-from .render import assemble_input_device, render_batch_device, render_concat_device
+from .render import assemble_input_device, gt_norm_u8_device, render_batch_device, render_concat_device
 from .step import RenderCompareStep
 
 __all__ = ["_lib", "mesh", "ops", "RacError", "launch_count", "lib", "assemble_input_device",
-           "render_batch_device", "render_concat_device", "RenderCompareStep", "sample_poses_device", "silhouette_device",
+           "render_batch_device", "render_concat_device", "gt_norm_u8_device", "RenderCompareStep", "sample_poses_device", "silhouette_device",
            "blend_device"]

@@ -60,6 +60,8 @@ SIGNATURES = {
                                  c_void_p, c_void_p, c_void_p]),
     "rac_silhouette": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "rac_blend": (c_int, [c_void_p, c_void_p, c_float, c_int, c_size_t, c_void_p, c_void_p]),
+    "rac_gt_u8_workspace_bytes": (c_size_t, [c_int]),
+    "rac_gt_norm_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
 }
 
 RAC_ROT = {"6D": 0, "SVD": 1, "3D": 2}

@@ -163,9 +163,9 @@ def _copy_stream(dev):
     return s
 
 
-def _gt_staging(dev, shape):
+def _gt_staging(dev, shape, dtype=torch.float32):
     """Ring of device staging buffers for uploaded gt crops; each entry carries the event of its last consumer."""
-    key = (dev.index, tuple(shape))
+    key = (dev.index, tuple(shape), dtype)
     ring = _gt_rings.get(key)
     if ring is None:
         ring = {"next": 0, "bufs": [None] * _GT_RING, "done": [None] * _GT_RING}
@@ -173,12 +173,12 @@ def _gt_staging(dev, shape):
     i = ring["next"]
     ring["next"] = (i + 1) % _GT_RING
     if ring["bufs"][i] is None:
-        ring["bufs"][i] = torch.empty(shape, dtype=torch.float32, device=dev)
+        ring["bufs"][i] = torch.empty(shape, dtype=dtype, device=dev)
     return ring, i
 
 
-def _overlappable(t):
-    return (isinstance(t, torch.Tensor) and t.device.type == "cpu" and t.dtype == torch.float32 and t.is_contiguous()
+def _overlappable(t, dtype=torch.float32):
+    return (isinstance(t, torch.Tensor) and t.device.type == "cpu" and t.dtype == dtype and t.is_contiguous()
             and t.dim() == 4 and t.is_pinned() and not torch.cuda.is_current_stream_capturing())
 
 
@@ -231,6 +231,48 @@ def _gt_cache_store(t, dev, planes):
     _gt_cache.append((weakref.ref(t), t.data_ptr(), t._version, tuple(t.shape), dev.index, planes.clone()))
 
 
+# ---- 8-bit gt crops ---------------------------------------------------------------------------------------------
+# A uint8 (B,H,W,3) crop is taken as the raw `real.png` codes: the `/ 255.0` of image_dataloaders.py:79-83 moves into
+# rac_gt_norm_u8, and the crop crosses PCIe at a quarter of the bytes of the f32 form.
+def _is_u8(t):
+    return (isinstance(t, torch.Tensor) and t.dtype == torch.uint8) or (isinstance(t, np.ndarray) and t.dtype == np.uint8)
+
+
+def gt_norm_u8_device(gt_u8, x, use_norm_depth=False):
+    """normalize_img(gt_u8 / 255.0) -> the three gt planes of x (B,C,H,W) f32 CUDA; gt_u8 (B,H,W,3) uint8, host or device.
+    A pinned host tensor is uploaded on the library's copy stream (it overlaps whatever the current stream is running)."""
+    L = _lib.lib()
+    dev = x.device
+    B, C, H, W = x.shape
+    assert C == (7 if use_norm_depth else 6) and tuple(gt_u8.shape) == (B, H, W, 3) and x.is_contiguous() and x.dtype == torch.float32
+    ring = None
+    if _overlappable(gt_u8, torch.uint8):
+        main = torch.cuda.current_stream(dev)
+        cs = _copy_stream(dev)
+        ring, slot = _gt_staging(dev, (B, H, W, 3), torch.uint8)
+        g = ring["bufs"][slot]
+        if ring["done"][slot] is not None:
+            cs.wait_event(ring["done"][slot])
+        with torch.cuda.stream(cs):
+            g.copy_(gt_u8, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(cs)
+        main.wait_event(ev)
+    else:
+        g = torch.as_tensor(gt_u8).to(device=dev).contiguous()
+    need = L.rac_gt_u8_workspace_bytes(B)
+    ws = _workspace(dev, need + 256)
+    base = (ws.data_ptr() + 255) // 256 * 256
+    rc = L.rac_gt_norm_u8(_lib.ptr(g), B, W, H, int(bool(use_norm_depth)), _lib.ptr(x), ctypes.c_void_p(base),
+                          ws.numel() - (base - ws.data_ptr()), _lib.stream_ptr())
+    _lib.check(rc)
+    if ring is not None:
+        done = torch.cuda.Event()
+        done.record(torch.cuda.current_stream(dev))
+        ring["done"][slot] = done
+    return x
+
+
 def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
     """prepare_model_input on renders that already exist (iteration 0): -> x (B,C,H,W) f32 CUDA."""
     L = _lib.lib()
@@ -248,6 +290,11 @@ def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
     if cached is not None:
         x[:, C - 3:].copy_(cached)
         _assemble_call(L, init, None, d, B, W, H, use_norm_depth, x, dev)
+        return x
+    if _is_u8(gt_hwc):
+        gt_norm_u8_device(gt_hwc, x, use_norm_depth)
+        _assemble_call(L, init, None, d, B, W, H, use_norm_depth, x, dev)
+        _gt_cache_store(gt_hwc, dev, x[:, C - 3:])
         return x
     if _overlappable(gt_hwc) and B >= 2 * _GT_CHUNKS:
         main = torch.cuda.current_stream(dev)

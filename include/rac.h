@@ -207,6 +207,17 @@ RAC_API int rac_silhouette(const float* d_img_hwc, int B, int W, int H, int silh
 RAC_API int rac_blend(const float* d_im1, const float* d_im2, float alpha, int quantized_inputs, size_t n,
                       float* d_out, rac_stream_t stream);
 
+/* ---- 8-bit gt crops ----------------------------------------------------------
+ * ref: image_dataloaders.py:79-83 (gt = real.png / 255.0, f64) followed by data_loaders.py:79-82 (normalize_img) and the
+ * f32 cast + HWC->CHW of data_loaders.py:163-166, computed from the raw 8-bit codes so that the crop crosses PCIe at
+ * 3 B/px instead of 12.  d_gt_hwc_u8 (B,H,W,3) u8 -> the three gt planes (channels C-3..C-1, C = 7 if use_norm_depth
+ * else 6) of d_x_nchw (B,C,H,W) f32; the other planes are not touched (rac_assemble_input / rac_render_concat with
+ * d_gt_hwc == NULL fill them).  Exact integer statistics, every output value = (float)((q/255.0 - mean)/std) evaluated
+ * in f64: bit-identical to the reference's cast.  d_stats_ws: rac_gt_u8_workspace_bytes(B) bytes, 8-byte aligned. */
+RAC_API size_t rac_gt_u8_workspace_bytes(int B);
+RAC_API int rac_gt_norm_u8(const unsigned char* d_gt_hwc_u8, int B, int W, int H, int use_norm_depth, float* d_x_nchw,
+                           void* d_stats_ws, size_t ws_bytes, rac_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -92,3 +92,73 @@ def test_visualization_module_and_blend(rac, gold):
     np.testing.assert_array_equal(q, np.round(gold["blend_f64_077"] * 255).astype(np.int64))
     with pytest.raises(AssertionError):
         rac.blend_device(a, b64, 1.5)
+
+
+# ---- 8-bit gt crops (rac_gt_norm_u8): image_dataloaders.py:79-83 + data_loaders.py:79-82 from the raw codes -------
+def _u8_crops(B, H, W, seed):
+    rng = np.random.default_rng(seed)
+    g = rng.integers(0, 256, (B, H, W, 3), dtype=np.uint8)
+    g[1] = rng.integers(100, 104, (H, W, 3), dtype=np.uint8)        # narrow range
+    g[2] = 0
+    g[2, H // 2, W // 2, 1] = 255                                   # one bright value in a black crop
+    return g
+
+
+@pytest.mark.parametrize("use_depth", [False, True])
+@pytest.mark.parametrize("W,H", [(320, 240), (99, 65), (32, 8)])
+def test_gt_u8_crop_matches_reference_cast(rac, use_depth, W, H):
+    """uint8 crop in, planes out == (normalize_img(u8 / 255.0)).astype(f32) of the oracle, bit for bit (exact integer
+    statistics + a per-image table evaluated in f64); the render / depth planes equal the f32-crop path's."""
+    from oracle import assemble_ref
+    B = 5
+    g = _u8_crops(B, H, W, seed=W)
+    rng = np.random.default_rng(1)
+    init = rng.uniform(0, 1, (B, H, W, 3)).astype(np.float32)
+    depth = np.where(rng.uniform(size=(B, H, W)) < 0.3, rng.uniform(2.0, 3.0, (B, H, W)), 0.0).astype(np.float32)
+    ref = assemble_ref.prepare_model_input(init, g.astype(np.float64) / 255.0, depth, use_depth).numpy()
+    c0 = 1 if use_depth else 0
+    for form in ("numpy", "device", "pinned"):
+        gt = g if form == "numpy" else torch.from_numpy(g).cuda() if form == "device" else torch.from_numpy(g).pin_memory()
+        x = rac.assemble_input_device(init, gt, depth if use_depth else None, use_depth).cpu().numpy()
+        assert x.shape == ref.shape
+        a, b = x[:, c0 + 3:], ref[:, c0 + 3:]
+        same = a.view(np.uint32) == b.view(np.uint32)
+        assert same.mean() > 0.9999, (form, same.mean())            # a table entry on a rounding boundary: <= 1 ulp
+        np.testing.assert_allclose(a, b, rtol=2e-7, atol=0)
+        x32 = rac.assemble_input_device(init, (g.astype(np.float64) / 255.0).astype(np.float32), depth if use_depth else None,
+                                        use_depth).cpu().numpy()
+        assert np.array_equal(x[:, :c0 + 3], x32[:, :c0 + 3])
+        # (full-range crops only: an f32 crop of a 4-level image has lost more than 1e-5 of its spread before any kernel runs)
+        np.testing.assert_allclose(a[[0, 3, 4]], x32[[0, 3, 4], c0 + 3:], rtol=1e-5, atol=2e-6)
+
+
+def test_gt_u8_constant_crop_is_nan_like_the_reference(rac):
+    """normalize_img has no zero-std guard (data_loaders.py:79-82): a constant crop is 0/0 = nan everywhere."""
+    g = np.full((2, 16, 32, 3), 77, dtype=np.uint8)
+    g[1, 0, 0, 0] = 78
+    init = np.zeros((2, 16, 32, 3), dtype=np.float32)
+    x = rac.assemble_input_device(init, g, None, False).cpu().numpy()
+    assert np.isnan(x[0, 3:]).all() and np.isfinite(x[1, 3:]).all() and np.array_equal(x[:, :3], np.zeros_like(x[:, :3]))
+
+
+def test_gt_u8_full_size_through_the_shadow_module(rac):
+    """data_loaders.prepare_model_input with a pinned uint8 crop at the bench size (B=64, 320x240): statistics of every
+    image are those of a normalised image (mean 0, std 1), planes equal the f32-crop path within the f32 bar, and the
+    call is repeatable (staging ring reuse)."""
+    import data_loaders as DL
+    B, H, W = 64, 240, 320
+    g = torch.from_numpy(np.random.default_rng(4).integers(0, 256, (B, H, W, 3), dtype=np.uint8)).pin_memory()
+    init = torch.rand((B, H, W, 3), device="cuda")
+    from rac import render as R
+    prev = R.set_gt_cache(False)        # every call uploads and normalises
+    try:
+        x1 = DL.prepare_model_input(init, g, None, False)
+        x2 = DL.prepare_model_input(init, g, None, False)
+    finally:
+        R.set_gt_cache(prev)
+    x3 = DL.prepare_model_input(init, (g.double() / 255.0).float().pin_memory(), None, False)
+    assert torch.equal(x1, x2)
+    gt = x1[:, 3:].double()
+    assert gt.mean(dim=(1, 2, 3)).abs().max() < 1e-6 and (gt.std(dim=(1, 2, 3), unbiased=False) - 1).abs().max() < 1e-6
+    assert torch.equal(x1[:, :3], x3[:, :3])
+    torch.testing.assert_close(x1[:, 3:], x3[:, 3:], rtol=1e-5, atol=2e-6)
