@@ -1,6 +1,6 @@
 """Where the end-to-end step (bench.py step_e2e: the reference-facing calls on pinned host buffers) spends its time:
 host enqueue time per call (no sync) and the synchronised total.  Diagnostic only.  Usage (GPU box):
-python profiles/e2e_breakdown.py"""
+python profiles/e2e_breakdown.py [--u8]   (--u8: the gt crop as uint8 codes, rac_gt_norm_u8)"""
 import os
 import sys
 import time
@@ -17,6 +17,8 @@ def main():
     import loss as L
     import rotation_representation as RR
     from rac import mesh as M
+    from rac import render as R
+    R.set_gt_cache(False)
     dev = torch.device("cuda", 0)
     mesh, sets, K = bench.make_inputs(seed=1000)
     B, W, H = bench.B, bench.W, bench.H
@@ -26,7 +28,7 @@ def main():
     Ks = torch.tensor(K)
     hs = []
     for s in sets:
-        hs.append(dict(gt=torch.rand((B, H, W, 3)).pin_memory(), T=torch.tensor(s["T_init"]).pin_memory(),
+        hs.append(dict(gt=(torch.randint(0, 256, (B, H, W, 3), dtype=torch.uint8) if "--u8" in sys.argv else torch.rand((B, H, W, 3))).pin_memory(), T=torch.tensor(s["T_init"]).pin_memory(),
                        Tg=torch.tensor(s["T_gt"]).pin_memory(), y=torch.tensor(s["y"]).pin_memory(),
                        pts=torch.tensor(s["pts"]).pin_memory()))
     h_pose = torch.empty((B, 4, 4)).pin_memory()
