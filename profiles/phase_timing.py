@@ -61,4 +61,6 @@ def per_class(tot, cls_n):
 
 
 if __name__ == "__main__":
-    per_class(*main())
+    res = main()
+    if res is not None:      # (--build-only returns nothing)
+        per_class(*res)
