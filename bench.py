@@ -357,7 +357,7 @@ def run_ours(args):
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(seconds=15.0)
-        print(json.dumps(out), flush=True)
+        emit_result(out)
     if world > 1:
         dist.destroy_process_group()
 
@@ -435,7 +435,18 @@ def run_reference(args):
            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
-    print(json.dumps(out), flush=True)
+    emit_result(out)
+
+
+_RESULT_FD = None
+
+
+def emit_result(out):
+    line = (json.dumps(out) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(line.decode()); sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, line)
 
 
 def main():
@@ -446,6 +457,12 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~15 s CPU oracle leg (profiling runs)")
     args = ap.parse_args()
+    # stdout carries exactly one JSON line: everything else that native libraries print there (NCCL's version banner
+    # under torchrun) is sent to stderr by pointing fd 1 at fd 2 and keeping the real stdout for the result line
+    global _RESULT_FD
+    sys.stdout.flush()
+    _RESULT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         # torchrun exports OMP_NUM_THREADS=1 to every rank; the reference arm runs on rank 0 alone and is meant to use
         # every host core, so undo that before libgomp is loaded (by torch / the oracle library)
