@@ -120,3 +120,27 @@ def test_camera_matrix_and_lazy_array():
     np.testing.assert_array_equal(a[1], t.numpy()[1])
     assert float(np.max(a)) == 23.0 and (a / 2)[0, 0, 2] == 1.0
     assert torch.tensor(np.asarray(a)).shape == (2, 3, 4)      # train_model.py:241 pattern
+
+
+def test_bench_reference_arm_prints_one_json_line():
+    """bench.py --impl reference (the oracle port on the host cores): stdout is exactly one JSON line with the
+    contract's keys; under a multi-rank launch only rank 0 runs and the other ranks exit 0 without output."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1"]
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    res = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=600)
+    assert res.returncode == 0, res.stderr[-2000:]
+    lines = [l for l in res.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, res.stdout
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["unit"] == "renders/s" and d["higher_is_better"] is True and d["value"] > 0
+    assert d["steps"] == 1 and d["n_gpus"] == 1 and "workload" in d["config"]
+    cb = d["cpu_baseline"]
+    assert cb["kind"] == "port" and cb["cores"] >= 1 and cb["value"] == d["value"] and cb["sample"]
+    assert d["e2e"] == {"value": d["value"], "unit": d["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    env2 = dict(env, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
+    res2 = subprocess.run(cmd, capture_output=True, text=True, env=env2, timeout=600)
+    assert res2.returncode == 0 and res2.stdout.strip() == "", (res2.returncode, res2.stdout, res2.stderr[-500:])
