@@ -78,7 +78,7 @@ static int raster_grid() {
     }
     return g_raster_grid;
 }
-constexpr int kMaxRasterGrid = 256 * 4;     // workspace is sized for this many CTAs (no device query in the size function)
+constexpr int kMaxRasterGrid = 256 * 4;     // upper bound of the persistent grid (SMs x resident CTAs)
 
 static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
     RenderWs w;
@@ -99,7 +99,6 @@ static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
     w.recs = (int4*)(p + off);               off = align256(off + sizeof(int4) * 3 * (size_t)B * maxT);
     w.desc = (unsigned*)(p + off);           off = align256(off + sizeof(unsigned) * ndesc);
     w.refs = (unsigned char*)(p + off);      off = align256(off + nrefs);
-    w.scratch_col = (unsigned*)(p + off);    off = align256(off + sizeof(unsigned) * kScratchPerCta * (size_t)kMaxRasterGrid);
     w.rgba = (unsigned*)(p + off);           off = align256(off + sizeof(unsigned) * (size_t)B * W * H);
     w.depth = (float*)(p + off);             off = align256(off + sizeof(float) * (size_t)B * W * H);
     w.total = off;
@@ -311,7 +310,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         raster_kernel<<<grid, kRasterThreads, kRasterSmemBytes, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,
                                                                           ws.stats, ws.large_cnt, ws.large_tri, ws.recs, ws.desc, ws.refs,
                                                                           ws.ctl, ws.buckets, (size_t)B * tg.nt, ws.rgba,
-                                                                          (fin.depth_out || (fin.x_nchw && fin.use_norm_depth)) ? ws.depth : (float*)nullptr, ws.scratch_col,
+                                                                          (fin.depth_out || (fin.x_nchw && fin.use_norm_depth)) ? ws.depth : (float*)nullptr,
                                                                           (fin.x_nchw && fin.use_norm_depth) ? 1 : 0);
         RAC_LAUNCHED();
     }

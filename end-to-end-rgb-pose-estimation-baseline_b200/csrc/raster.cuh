@@ -83,7 +83,6 @@ struct RenderWs {
     WorkCtl* ctl;          // work-list counters (zeroed with stats and loads by one memset)
     unsigned* loads;       // [B][nt] load estimate of the bin (0 = empty bin)
     unsigned* buckets;     // [kBuckets][B * nt] non-empty bins (image * nt + bin) by load class
-    unsigned* scratch_col; // [raster CTAs][4][512] committed colours of bins with more than 254 triangles
     unsigned* rgba;        // [B][H][W] resolved RGBA8 (non-empty bins only)
     float* depth;          // [B][H][W] metric depth (non-empty bins only)
     size_t zero_bytes;     // bytes from `stats` that every call zeroes (stats + ctl + loads)

@@ -12,7 +12,7 @@
 //             256 per step (flattened again), colours averaged, RGBA8 + f32 depth stored as 128-B row segments, and
 //             the per-image max / depth statistics reduced -> one atomic per accumulator per bin.
 // A bin with more than 254 triangles commits between batches: the current winners are shaded, their colours parked in
-// the CTA's global scratch and their ids cleared (id 0 = committed: a later triangle at the same depth loses, as
+// the shared-memory colour buffer of the resolve (at the samples they won) and their ids cleared (id 0 = committed: a later triangle at the same depth loses, as
 // in-order rasterisation would have it).  The warp-autonomous alternative (one warp per 16x8 sub-tile, no barriers)
 // was built and measured slower: see profiles/README.md.
 
@@ -46,7 +46,6 @@ constexpr int kSmallPix = RAC_SMALL_PIX;   // bbox∩bin pixels handled as flatt
 constexpr int kTilePix = kTileW * kTileH;
 constexpr int kTriStride = 20;        // words per staged triangle (16 used; 80 B keeps LDS.128 aligned and conflict-free)
 constexpr unsigned kKeyEmpty32 = 0xFFFFFFFFu;
-constexpr int kScratchPerCta = 4 * kTilePix;     // u32 colours of committed samples (global, per persistent CTA)
 
 // dynamic shared memory of one CTA
 struct __align__(16) RasterSmem {
@@ -264,11 +263,13 @@ struct TileAcc {
 // (pixel, representative sample) item per distinct triangle; R2: the items are shaded 256 at a time (no lane idles on
 // background or waits for a neighbour's 4-triangle edge pixel); R3 (FINAL): every pixel averages its samples' colours
 // through the representatives / the committed colours and stores RGBA8 + depth.
-// FINAL = false (commit): R2 parks the colours in the CTA's global scratch and clears the ids; no R3.
+// FINAL = false (commit): R2 parks the colours in `cols`, at the samples the triangle won, and clears the ids; no R3.
+// (`cols` is written again only by the final R2, and only at representative samples of live ids, so a parked colour
+// survives exactly as long as its sample does.)
 // Called by all threads; q_count is a zeroed shared counter (left zeroed).
 template <bool FINAL>
 __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const BinCtx& bc,
-                                            unsigned* __restrict__ scratch_col, const ShadeCtx* s_sc,
+                                            const ShadeCtx* s_sc,
                                             const SceneConsts& S, unsigned* __restrict__ rgba_out,
                                             float* __restrict__ depth_out, size_t img_pix, int W, TileAcc& acc, int need_dstats
                                             RAC_PHASE_ARGS) {
@@ -340,7 +341,8 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
                 for (int s2 = 0; s2 < 4; ++s2) {
                     const unsigned k2 = sm.z[s2 * kTilePix + p];
                     if (s2 >= s && k2 != kKeyEmpty32 && ((k2 ^ key) & 0xFFu) == 0u) {
-                        scratch_col[s2 * kTilePix + p] = col;
+                        cols[s2 * kTilePix + p] = col;     // stays there: only the final resolve writes cols again, and only
+                                                           // at representative samples of live ids
                         sm.z[s2 * kTilePix + p] = k2 & ~0xFFu;
                     }
                 }
@@ -375,7 +377,7 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
             if (k[s] == kKeyEmpty32) continue;
             unsigned col;
             if ((k[s] & 0xFFu) == 0u) {
-                col = __ldcg(scratch_col + s * kTilePix + p);          // committed earlier
+                col = cols[s * kTilePix + p];          // committed earlier: parked in place by the commit
             } else {
                 int rep = s;
 #pragma unroll
@@ -403,10 +405,10 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
 }
 
 // commit (rare: more than 254 triangles in a bin) — out of line, so that the hot path carries one copy of the resolve
-__device__ __noinline__ void commit_bin(RasterSmem& sm, int* q_count, const BinCtx& bc, unsigned* __restrict__ scratch_col,
+__device__ __noinline__ void commit_bin(RasterSmem& sm, int* q_count, const BinCtx& bc,
                                         const ShadeCtx* s_sc, const SceneConsts& S RAC_PHASE_ARGS) {
     TileAcc dummy;
-    resolve_bin<false>(sm, q_count, bc, scratch_col, s_sc, S, nullptr, nullptr, 0, 0, dummy, 0 RAC_PHASE_PASS);
+    resolve_bin<false>(sm, q_count, bc, s_sc, S, nullptr, nullptr, 0, 0, dummy, 0 RAC_PHASE_PASS);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -414,7 +416,7 @@ __device__ __noinline__ void commit_bin(RasterSmem& sm, int* q_count, const BinC
 // ---------------------------------------------------------------------------------------------
 // s_ctl: [0] resolve item count, [1], [2] medium-triangle counts of alternating batches (all zero on entry and on exit);
 // s_scan: [4 * kRasterThreads + 8] descriptor counts / scan / offsets / large counts / warp sums.
-__device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned* s_scan, ShadeCtx* s_sc, unsigned* __restrict__ scratch_col,
+__device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned* s_scan, ShadeCtx* s_sc,
                                             const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids,
                                             int uniform_mesh, const float* __restrict__ T_CO, const float* __restrict__ K,
                                             int W, int H, int maxT, const TileGrid& tg, const SceneConsts& S,
@@ -464,7 +466,7 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
         for (int qb = 0; qb < qn; qb += kBatch) {
             const int n = min(kBatch, qn - qb);
             if (nslots + n > kBatch) {
-                commit_bin(sm, q_count, bc, scratch_col, s_sc, S RAC_PHASE_PASS);
+                commit_bin(sm, q_count, bc, s_sc, S RAC_PHASE_PASS);
                 nslots = 0;
             }
             process_batch<LARGE>(sm, med_count + (batch_no & 1), s_wsum, bc, sm.queue + qb, n, (unsigned)nslots + 1u RAC_PHASE_PASS);
@@ -582,7 +584,7 @@ __device__ __forceinline__ void raster_tile(RasterSmem& sm, int* s_ctl, unsigned
     // ---- resolve + shade + write, and per-image accumulators ----
     TileAcc acc;
     acc.qmax = 0; acc.dcount = 0; acc.dmax = 0.0f; acc.dsum = 0.0; acc.dsumsq = 0.0;
-    resolve_bin<true>(sm, q_count, bc, scratch_col, s_sc, S, rgba_out, depth_out, img_pix, W, acc, need_dstats RAC_PHASE_PASS);
+    resolve_bin<true>(sm, q_count, bc, s_sc, S, rgba_out, depth_out, img_pix, W, acc, need_dstats RAC_PHASE_PASS);
     RAC_PHASE(10);
     // block reduction -> one atomic per accumulator per CTA
     __shared__ double red_d[2][kRasterWarpsN];
@@ -623,7 +625,7 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
               SceneConsts S, ImgStats* __restrict__ stats, const unsigned* __restrict__ large_cnt,
               const unsigned* __restrict__ large_tri, const int4* __restrict__ recs, const unsigned* __restrict__ desc,
               const unsigned char* __restrict__ refs, WorkCtl* __restrict__ ctl, const unsigned* __restrict__ buckets,
-              size_t bucket_cap, unsigned* __restrict__ rgba_out, float* __restrict__ depth_out, unsigned* __restrict__ scratch_col,
+              size_t bucket_cap, unsigned* __restrict__ rgba_out, float* __restrict__ depth_out,
               int need_dstats) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RasterSmem& sm = *reinterpret_cast<RasterSmem*>(smem_raw);
@@ -635,7 +637,6 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
     unsigned first_ticket = 0;                       // requested before the bucket counts: the two L2 round trips overlap
     if (threadIdx.x == 0) first_ticket = atomicAdd(&ctl->next, 1u);
     load_bucket_prefix(ctl, s_prefix);               // final: written by setup_kernel (previous launch)
-    unsigned* my_scratch = scratch_col + (size_t)blockIdx.x * kScratchPerCta;
 #ifdef RAC_PHASE_TIMING
     WorkCtl* g_phase_ctl = ctl;
     long long g_phase_t = clock64();
@@ -671,7 +672,7 @@ raster_kernel(const MeshDev* __restrict__ table, const int* __restrict__ mesh_id
         unsigned r_next = 0;
         if (threadIdx.x == 0) r_next = atomicAdd(&ctl->next, 1u);   // parked in s_next before the resolve
         RAC_PHASE(0);
-        raster_tile(sm, s_ctl, s_scan, &s_sc, my_scratch, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_cnt,
+        raster_tile(sm, s_ctl, s_scan, &s_sc, table, mesh_ids, uniform_mesh, T_CO, K, W, H, maxT, tg, S, stats, large_cnt,
                     large_tri, recs, desc, refs, rgba_out, depth_out, (int)(e / (unsigned)tg.nt), (int)(e % (unsigned)tg.nt),
                     r_next, n_work, s_prefix, buckets, bucket_cap, s_next, need_dstats RAC_PHASE_PASS);
         RAC_PHASE(11);
