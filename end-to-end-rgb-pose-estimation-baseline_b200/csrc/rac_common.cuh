@@ -47,11 +47,14 @@ extern std::atomic<long long> g_launches;
 // a parallel graph branch next to the resident raster CTAs instead of waiting for an SM to drain.
 #define RAC_MAX_CARVEOUT_ONCE(kernel)                                                                       \
     do {                                                                                                    \
-        static bool _done = false;                                                                          \
-        if (!_done) {                                                                                       \
+        static std::atomic<unsigned long long> _done{0};      /* bit per device ordinal */                  \
+        int _dev = 0;                                                                                       \
+        RAC_CUDA_CHECK(cudaGetDevice(&_dev));                                                               \
+        const unsigned long long _bit = 1ull << (_dev & 63);                                                \
+        if (!(_done.load(std::memory_order_acquire) & _bit)) {                                              \
             RAC_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,     \
                                                 cudaSharedmemCarveoutMaxShared));                           \
-            _done = true;                                                                                   \
+            _done.fetch_or(_bit, std::memory_order_release);                                                \
         }                                                                                                   \
     } while (0)
 

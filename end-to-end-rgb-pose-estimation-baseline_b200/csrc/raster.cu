@@ -64,20 +64,6 @@ static TileGrid make_tile_grid(int W, int H, int maxT) {
     return tg;
 }
 
-static int g_raster_grid = 0;      // persistent raster CTAs (SMs x resident CTAs), fixed per process after the first query
-
-static int raster_grid() {
-    if (!g_raster_grid) {
-        int dev = 0, n_sm = 0, per_sm = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess) return 0;
-        if (cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
-        if (cudaFuncSetAttribute(raster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRasterSmemBytes) != cudaSuccess) return 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, raster_kernel, kRasterThreads, kRasterSmemBytes) != cudaSuccess) return 0;
-        if (per_sm < 1) per_sm = 1;
-        g_raster_grid = n_sm * per_sm;
-    }
-    return g_raster_grid;
-}
 constexpr int kMaxRasterGrid = 256 * 4;     // upper bound of the persistent grid (SMs x resident CTAs)
 
 static RenderWs carve_ws(void* base, int B, int W, int H, int maxT) {
@@ -126,44 +112,25 @@ static SceneConsts make_scene_consts(const rac_scene_t* scene) {
     return c;
 }
 
-// pinned staging ring for the per-image mesh-id table (only used when a batch mixes meshes)
-struct IdStage {
-    int* h = nullptr;
-    size_t cap = 0;
-    cudaEvent_t ev = nullptr;
-    bool pending = false;
-};
+// Per-image mesh-id table of a mixed-mesh batch: handed to the device BY VALUE, as kernel parameters (512 ids per
+// launch).  Nothing host-side outlives the call — no staging buffer to pool, reuse or leak, and a captured call keeps
+// its ids inside the graph's kernel node (a memcpy node would keep a pointer into caller memory instead).
+struct IdChunk { int v[512]; };
+__global__ void mesh_ids_kernel(int* __restrict__ dst, const __grid_constant__ IdChunk c, int n) {
+    const int i = (int)threadIdx.x;
+    if (i < n) dst[i] = c.v[i];
+}
 static std::mutex g_stage_mu;
-static IdStage g_stage[8];
-static int g_stage_next = 0;
 
 static int upload_ids(const int32_t* h_ids, int B, int* d_dst, cudaStream_t stream) {
-    std::lock_guard<std::mutex> lk(g_stage_mu);
-    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-    RAC_CUDA_CHECK(cudaStreamIsCapturing(stream, &cap));
-    if (cap != cudaStreamCaptureStatusNone) {
-        // graph capture: the memcpy node keeps the source pointer, so it gets a buffer of its own that is never
-        // reused (B ints per captured call, lives as long as the process)
-        int* h = nullptr;
-        RAC_CUDA_CHECK(cudaMallocHost(&h, sizeof(int) * (size_t)B));
-        for (int i = 0; i < B; ++i) h[i] = h_ids[i];
-        RAC_CUDA_CHECK(cudaMemcpyAsync(d_dst, h, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice, stream));
-        return RAC_OK;
+    for (int base = 0; base < B; base += 512) {
+        IdChunk c;
+        const int n = B - base < 512 ? B - base : 512;
+        for (int i = 0; i < n; ++i) c.v[i] = h_ids[base + i];
+        for (int i = n; i < 512; ++i) c.v[i] = 0;
+        mesh_ids_kernel<<<1, 512, 0, stream>>>(d_dst + base, c, n);
+        RAC_LAUNCHED();
     }
-    IdStage& st = g_stage[g_stage_next];
-    g_stage_next = (g_stage_next + 1) % 8;
-    if (st.pending) { RAC_CUDA_CHECK(cudaEventSynchronize(st.ev)); st.pending = false; }
-    if (st.cap < (size_t)B) {
-        if (st.h) RAC_CUDA_CHECK(cudaFreeHost(st.h));
-        st.h = nullptr; st.cap = 0;
-        RAC_CUDA_CHECK(cudaMallocHost(&st.h, sizeof(int) * (size_t)B));
-        st.cap = (size_t)B;
-    }
-    if (!st.ev) RAC_CUDA_CHECK(cudaEventCreateWithFlags(&st.ev, cudaEventDisableTiming));
-    for (int i = 0; i < B; ++i) st.h[i] = h_ids[i];
-    RAC_CUDA_CHECK(cudaMemcpyAsync(d_dst, st.h, sizeof(int) * (size_t)B, cudaMemcpyHostToDevice, stream));
-    RAC_CUDA_CHECK(cudaEventRecord(st.ev, stream));
-    st.pending = true;
     return RAC_OK;
 }
 
@@ -175,9 +142,14 @@ static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 struct SideStream {
     cudaStream_t stream = nullptr;
     cudaEvent_t fork = nullptr, join = nullptr;
+    int n_sm = 0;              // per device: a process may drive several GPUs
+    int raster_grid = 0;       // persistent raster CTAs (SMs x resident CTAs)
 };
 static SideStream g_side[64];
 
+// Per-device state of the render path (created on first use, under g_stage_mu): the side stream and its events, the
+// SM count, the persistent raster grid, and the L1 / shared-memory carve-out of every kernel of the call (an SM does
+// not mix carve-outs, so the forked gt kernel and the main chain ask for raster_kernel's split).
 static int side_stream(SideStream** out) {
     int dev = 0;
     RAC_CUDA_CHECK(cudaGetDevice(&dev));
@@ -185,9 +157,18 @@ static int side_stream(SideStream** out) {
     std::lock_guard<std::mutex> lk(g_stage_mu);
     SideStream& s = g_side[dev];
     if (!s.stream) {
-        RAC_CUDA_CHECK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+        int per_sm = 0;
+        RAC_CUDA_CHECK(cudaDeviceGetAttribute(&s.n_sm, cudaDevAttrMultiProcessorCount, dev));
+        RAC_CUDA_CHECK(cudaFuncSetAttribute(raster_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kRasterSmemBytes));
+        RAC_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, raster_kernel, kRasterThreads, kRasterSmemBytes));
+        if (per_sm < 1) per_sm = 1;
+        s.raster_grid = s.n_sm * per_sm;
+        RAC_CUDA_CHECK(cudaFuncSetAttribute(setup_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        RAC_CUDA_CHECK(cudaFuncSetAttribute(finalize_live_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        RAC_CUDA_CHECK(cudaFuncSetAttribute(gt_norm_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         RAC_CUDA_CHECK(cudaEventCreateWithFlags(&s.fork, cudaEventDisableTiming));
         RAC_CUDA_CHECK(cudaEventCreateWithFlags(&s.join, cudaEventDisableTiming));
+        RAC_CUDA_CHECK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));     // (last: marks the slot ready)
     }
     *out = &s;
     return RAC_OK;
@@ -234,17 +215,12 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
     // Side work — everything that does not depend on the render: the gt half of the concat (+ zero background of the
     // render planes of x) and the zero background of the other outputs.  It runs on a forked stream under
     // setup_kernel / raster_kernel and is joined before finalize_live_kernel overwrites the non-empty tiles.
-    static int n_sm = 0;
-    if (!n_sm) {
-        int dev = 0;
-        RAC_CUDA_CHECK(cudaGetDevice(&dev));
-        RAC_CUDA_CHECK(cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev));
-    }
     SideStream* side = nullptr;
     {
         int rc = side_stream(&side);
         if (rc != RAC_OK) return rc;
     }
+    const int n_sm = side->n_sm;
     cudaStream_t sstream = (skip & 16) ? stream : side->stream;
     const TileGrid tg = make_tile_grid(W, H, maxT);
     // Concat-only calls (no depth / HWC / RGBA8 side outputs): the gt kernel leaves the quads of non-empty bins alone,
@@ -266,14 +242,6 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
         if (fin.rgba_copy) RAC_CUDA_CHECK(cudaMemsetAsync(fin.rgba_copy, 0, sizeof(unsigned) * npix * B, sstream));
         return RAC_OK;
     };
-    static bool carve_configured = false;
-    if (!carve_configured) {
-        // every kernel of the call uses raster_kernel's L1 / shared-memory split, so that CTAs of the forked kernel and
-        // of the main chain can share an SM (an SM does not mix carve-outs)
-        RAC_CUDA_CHECK(cudaFuncSetAttribute(setup_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        RAC_CUDA_CHECK(cudaFuncSetAttribute(finalize_live_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        carve_configured = true;
-    }
     const bool fork_early = (skip & 32) != 0;
     if (fork_early && !(skip & 16)) {
         RAC_CUDA_CHECK(cudaEventRecord(side->fork, stream));
@@ -304,7 +272,7 @@ static int render_common(const int32_t* h_mesh_ids, const float* d_T_CO, const f
     if (!fork_early || (skip & 16)) { int rc = side_work(); if (rc != RAC_OK) return rc; }
     if (!(skip & 16)) RAC_CUDA_CHECK(cudaEventRecord(side->join, side->stream));
     if (!(skip & 4)) {
-        const int grid_max = raster_grid();
+        const int grid_max = side->raster_grid;
         RAC_REQUIRE(grid_max > 0 && grid_max <= kMaxRasterGrid, "render: raster grid query failed (%d)", grid_max);
         const int grid = (int)min((long long)grid_max, (long long)B * tg.nt);
         raster_kernel<<<grid, kRasterThreads, kRasterSmemBytes, stream>>>(table, d_ids, h_mesh_ids[0], d_T_CO, d_K, W, H, maxT, tg, S,

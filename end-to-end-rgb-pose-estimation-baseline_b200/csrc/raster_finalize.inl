@@ -353,13 +353,7 @@ static int launch_gt_norm(const float* d_gt_hwc, float* d_x_nchw, int B, int npi
     const int C = use_norm_depth ? 7 : 6, ch0 = use_norm_depth ? 4 : 3;
     const int vec = (npix % 4 == 0 && (reinterpret_cast<uintptr_t>(d_gt_hwc) & 15u) == 0 &&
                      (reinterpret_cast<uintptr_t>(d_x_nchw) & 15u) == 0) ? 1 : 0;
-    // same L1 / shared-memory split as raster_kernel: an SM cannot host CTAs of two kernels that want different
-    // carve-outs, and the point of this kernel is to sit next to the raster CTAs
-    static bool configured = false;
-    if (!configured) {
-        RAC_CUDA_CHECK(cudaFuncSetAttribute(gt_norm_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        configured = true;
-    }
+    RAC_MAX_CARVEOUT_ONCE(gt_norm_kernel);     // (rac_assemble_input reaches this kernel without render_common)
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(kGtCluster, (n_clusters > 0 && n_clusters < B) ? n_clusters : B);
     cfg.blockDim = dim3(kGtThreads);

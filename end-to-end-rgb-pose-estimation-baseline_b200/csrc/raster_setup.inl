@@ -111,7 +111,7 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
     if (tg.binned)
         for (int i = tid; i < tg.nt; i += kSetupCtaThreads) s_cnt[i] = 0;
 
-    bool keep[kSetupPer];
+    bool keep[kSetupPer], fits32[kSetupPer];
     int tx0[kSetupPer], tx1[kSetupPer], ty0[kSetupPer], ty1[kSetupPer];
 #pragma unroll
     for (int k = 0; k < kSetupPer; ++k) {
@@ -119,7 +119,7 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
         keep[k] = t < T;
         int X0 = 0, Y0 = 0, X1 = 0, Y1 = 0, X2 = 0, Y2 = 0;
         float iz0 = 0.f, iz1 = 0.f, iz2 = 0.f;
-        tx0[k] = 0; tx1[k] = -1; ty0[k] = 0; ty1[k] = -1;
+        tx0[k] = 0; tx1[k] = -1; ty0[k] = 0; ty1[k] = -1; fits32[k] = false;
         if (keep[k]) {
             const int i0 = mesh.faces[3 * t], i1 = mesh.faces[3 * t + 1], i2 = mesh.faces[3 * t + 2];
             keep[k] = project_vertex(cam, mesh.verts + 3 * (size_t)i0, znear, X0, Y0, iz0);
@@ -138,6 +138,9 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
             const int px0 = max(ceil_div256(xmin - 224), 0), px1 = min(floor_div256(xmax - 32), W - 1);
             const int py0 = max(ceil_div256(ymin - 224), 0), py1 = min(floor_div256(ymax - 32), H - 1);
             keep[k] = (px0 <= px1) && (py0 <= py1);
+            // the UNCLIPPED extent decides whether int32 edge functions are exact: a triangle hanging off an image
+            // corner can have an on-screen bounding box of 2x2 bins and still span thousands of pixels
+            fits32[k] = (xmax - xmin) <= 64 * kSubpix && (ymax - ymin) <= 64 * kSubpix;
             tx0[k] = px0 / kTileW; tx1[k] = px1 / kTileW; ty0[k] = py0 / kTileH; ty1[k] = py1 / kTileH;
         }
         if (keep[k]) {
@@ -160,11 +163,12 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
             r[2] = make_int4(__float_as_int(gy), __float_as_int(nx), __float_as_int(ny), __float_as_int(nz));
         }
     }
-    // binned: at most 2x2 bins (extent <= 64 px keeps the raster's edge functions inside int32)
+    // binned: at most 2x2 bins and an unclipped extent of at most 64 px (every edge-function product < 2^28: int32-exact);
+    // everything else takes the large list (int64 edge functions)
     bool small[kSetupPer], large[kSetupPer];
 #pragma unroll
     for (int k = 0; k < kSetupPer; ++k) {
-        small[k] = keep[k] && tg.binned && (tx1[k] - tx0[k] <= 1) && (ty1[k] - ty0[k] <= 1);
+        small[k] = keep[k] && tg.binned && fits32[k] && (tx1[k] - tx0[k] <= 1) && (ty1[k] - ty0[k] <= 1);
         large[k] = keep[k] && !small[k];
     }
     __syncthreads();   // s_cnt zeroed

@@ -201,6 +201,35 @@ def test_edge_cases(rac):
     np.testing.assert_allclose(centre, 2.5 - 0.15, rtol=2e-5)
 
 
+def test_big_faces_hanging_off_a_corner(rac):
+    """A 12-triangle box close to the camera, placed so that its faces leave the image at a corner: the ON-SCREEN bounding
+    box of such a face is at most 2x2 bins while the face itself spans hundreds of pixels.  Those triangles must take the
+    int64 path (their edge functions overflow int32); coverage and depth are compared bit for bit with the oracle."""
+    m = meshes()["box"]
+    W, H = 320, 240
+    rng = np.random.default_rng(3)
+    cands = []
+    for b in range(48):      # all four corners, the box centre 0.45 .. 0.62 m off axis at 0.75 m
+        cands.append(((1 if b & 1 else -1) * rng.uniform(0.45, 0.62), (1 if b & 2 else -1) * rng.uniform(0.42, 0.58)))
+    B = len(cands)
+    K = intrinsics(B, W, H)
+    T = np.tile(np.eye(4, dtype=np.float32), (B, 1, 1))
+    rng = np.random.default_rng(4)
+    for b, (sx, sy) in enumerate(cands):
+        a = rng.normal(size=3); a /= np.linalg.norm(a)
+        th = 0.5 * b
+        Kx = np.array([[0, -a[2], a[1]], [a[2], 0, -a[0]], [-a[1], a[0], 0]])
+        T[b, :3, :3] = np.eye(3) + np.sin(th) * Kx + (1 - np.cos(th)) * Kx @ Kx
+        T[b, :3, 3] = [sx, sy, 0.75]
+    out = rac.render_batch_device(T, m, K, (W, H), want_rgba8=True)
+    orc = ro.render_batch(m, T, K, (W, H))
+    compare(out, orc, W, H, "corner")
+    d = out["depth"].cpu().numpy()
+    cnt = (orc[1] > 0).reshape(B, -1).sum(1)
+    assert ((cnt > 30) & (cnt < 1200)).sum() >= 8, "several placements must leave only a small corner of a face on screen"
+    assert (d == orc[1]).all(), "depth / coverage must be bit-identical (int64 edge functions for clipped big faces)"
+
+
 @pytest.mark.parametrize("use_depth", [False, True])
 @pytest.mark.parametrize("W,H", [(320, 240), (99, 65)])
 def test_render_concat_matches_oracle_pipeline(rac, use_depth, W, H):
