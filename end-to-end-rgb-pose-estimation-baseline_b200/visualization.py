@@ -1,8 +1,18 @@
 """Drop-in for the per-pixel half of the reference's visualization.py: create_silhouette (ref:
 visualization.py:19-31) and blend_imgs (:34-37), the only per-pixel host loops left in validation /
 visualisation once rendering is on the GPU.  Same signatures, numpy in / numpy out;
-the work runs as CUDA kernels (csrc/aux_kernels.cu), there is no CPU path.  Figure assembly and file
-output (matplotlib / cv2, :43-201) stay the reference's."""
+the work runs as CUDA kernels (csrc/aux_kernels.cu), there is no CPU path.
+
+Figure assembly and file output (matplotlib / cv2, :43-201: save_img, create_interpolated_image_fig,
+visualize_examples, ...) stay the reference's: because this directory sits AHEAD of the reference on sys.path,
+`from visualization import visualize_examples` (train_model.py:13) and `create_interpolated_image_fig`
+(test_model.py:13) resolve here, so this module loads the reference's own visualization.py — the next one on
+sys.path — as an overlay base, re-exports everything it defines, and swaps its create_silhouette / blend_imgs
+for the two functions below (inside the reference module too, so its figure code calls the CUDA versions)."""
+import importlib.util
+import os
+import sys
+
 import numpy as np
 
 import rac
@@ -23,3 +33,26 @@ def create_silhouette(img, silhouette_only=False):
 def blend_imgs(im1, im2, alpha):
     """np.asarray(Image.blend(uint8(im1*255), uint8(im2*255), alpha)) / 255.0 -> f64 ndarray."""
     return rac.blend_device(im1, im2, alpha).cpu().numpy().astype(np.float64)
+
+
+def _overlay_reference():
+    """Load the reference's visualization.py (first one on sys.path that is not this file) and re-export it."""
+    here = os.path.dirname(os.path.abspath(__file__))
+    for entry in sys.path:
+        d = os.path.abspath(entry or os.getcwd())
+        cand = os.path.join(d, "visualization.py")
+        if d == here or not os.path.isfile(cand):
+            continue
+        spec = importlib.util.spec_from_file_location("_reference_visualization", cand)
+        ref = importlib.util.module_from_spec(spec)
+        sys.modules["_reference_visualization"] = ref
+        spec.loader.exec_module(ref)
+        ref.create_silhouette, ref.blend_imgs = create_silhouette, blend_imgs
+        for name, val in vars(ref).items():
+            if not name.startswith("__") and name not in ("create_silhouette", "blend_imgs"):
+                globals().setdefault(name, val)
+        return ref
+    return None
+
+
+_reference = _overlay_reference()

@@ -12,6 +12,9 @@ for p in (PKG, ROOT, GOLDEN):
         sys.path.insert(0, p)
 
 
+collect_ignore = ["ref_drivers"]      # the reference's own test_model.py lives there as a fixture, not as a test
+
+
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
 

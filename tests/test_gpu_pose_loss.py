@@ -210,3 +210,43 @@ def test_cpu_tensors_are_staged_through_the_gpu(mods):
     assert y.grad is not None and torch.isfinite(y.grad).all()
     ref = R.add_l1(T_gt, R.pose_update(y.detach(), T_in, "6D", Ks), pts)
     np.testing.assert_allclose(l.item(), ref.item(), rtol=1e-5)
+
+
+def test_q9_zero_length_6d_vector():
+    """Q9 (rotation_representation.py:9-10: no epsilon in the 6D normalisation).  A zero first column gives the reference a
+    nan rotation for THAT sample, a nan loss for that sample, nan gradients in that sample's six rotation inputs, and — under
+    torch.autograd.set_detect_anomaly(True), which train_model.py:18 switches on — a RuntimeError in backward.  Checked
+    live against the reference in the build container; restated here against the pinned oracle."""
+    import loss as L
+    import rotation_representation as RR
+    B, N = 4, 50
+    rng = np.random.default_rng(9)
+    y = rng.normal(size=(B, 9)).astype(np.float32)
+    y[1, :3] = 0.0
+    y[:, 8] = 1.0
+    T = np.tile(np.eye(4, dtype=np.float32), (B, 1, 1)); T[:, 2, 3] = 2.5
+    K = np.tile(np.array([[444.0, 0, 160], [0, 444.0, 120], [0, 0, 1]], np.float32), (B, 1, 1))
+    pts = rng.normal(size=(B, N, 3)).astype(np.float32)
+    yg = torch.tensor(y, device="cuda", requires_grad=True)
+    Tn = RR.calculate_T_CO_pred(yg, torch.tensor(T).cuda(), "6D", torch.tensor(K))
+    l = L.compute_ADD_L1_loss(torch.tensor(T).cuda(), Tn, torch.tensor(pts).cuda(), use_batch_mean=False)
+    yc = torch.tensor(y, requires_grad=True)
+    Tc = R.pose_update(yc, torch.tensor(T), "6D", torch.tensor(K))
+    lc = R.add_l1(torch.tensor(T), Tc, torch.tensor(pts), batch_mean=False)
+    Tn_h, l_h = Tn.detach().cpu().numpy(), l.detach().cpu().numpy()
+    assert np.isnan(Tn_h[1, :3, :3]).all() and np.isnan(Tc.detach().numpy()[1, :3, :3]).all()
+    assert np.isnan(l_h[1]) and np.isnan(lc.detach().numpy()[1])
+    ok = [0, 2, 3]
+    np.testing.assert_allclose(Tn_h[ok], Tc.detach().numpy()[ok], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(l_h[ok], lc.detach().numpy()[ok], rtol=1e-5)
+    l[0].backward(retain_graph=True)
+    lc[0].backward(retain_graph=True)
+    g, gc = yg.grad.cpu().numpy(), yc.grad.numpy()
+    np.testing.assert_allclose(g[ok], gc[ok], rtol=5e-4, atol=1e-6)
+    assert np.isnan(gc[1, :6]).all(), "reference: 0 * nan through the normalisation"
+    assert np.isnan(g[1, :6]).all(), "the zero-length sample's rotation gradients must be nan, as in the reference"
+    with pytest.raises(RuntimeError):
+        with torch.autograd.detect_anomaly():
+            y2 = torch.tensor(y, device="cuda", requires_grad=True)
+            T2 = RR.calculate_T_CO_pred(y2, torch.tensor(T).cuda(), "6D", torch.tensor(K))
+            L.compute_ADD_L1_loss(torch.tensor(T).cuda(), T2, torch.tensor(pts).cuda()).backward()
