@@ -62,6 +62,7 @@ SIGNATURES = {
     "rac_blend": (c_int, [c_void_p, c_void_p, c_float, c_int, c_size_t, c_void_p, c_void_p]),
     "rac_gt_u8_workspace_bytes": (c_size_t, [c_int]),
     "rac_gt_norm_u8": (c_int, [c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "rac_host_pack_gt_u8": (c_int, [c_void_p, c_int, c_size_t, c_void_p, c_int, ctypes.POINTER(c_int)]),
 }
 
 RAC_ROT = {"6D": 0, "SVD": 1, "3D": 2}

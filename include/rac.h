@@ -218,6 +218,16 @@ RAC_API size_t rac_gt_u8_workspace_bytes(int B);
 RAC_API int rac_gt_norm_u8(const unsigned char* d_gt_hwc_u8, int B, int W, int H, int use_norm_depth, float* d_x_nchw,
                            void* d_stats_ws, size_t ws_bytes, rac_stream_t stream);
 
+/* Host-side staging for the crop the unchanged loader produces (image_dataloaders.py:79-83: real.png / 255.0 — float64,
+ * pageable, 24 B/px for 3 B/px of information; handed to prepare_model_input at train_model.py:243 / test_model.py:100).
+ * One multi-threaded pass: h_dst[i] = q = rint(h_src[i] * 255) and *all_exact = 1 iff EVERY value equals q / 255.0 exactly
+ * (f64 source) or (float)(q / 255.0) (f32 source).  h_src: n floats or doubles (host); h_dst: n bytes (host, typically
+ * pinned).  When all_exact, h_dst feeds rac_gt_norm_u8 and the result is bit-identical to normalising the floats the
+ * reference's way; otherwise the caller uploads the floats.  n_threads <= 0: hardware concurrency, at most 16.
+ * No device work, no stream: data staging only (every normalisation still runs on the GPU). */
+RAC_API int rac_host_pack_gt_u8(const void* h_src, int src_is_f64, size_t n, unsigned char* h_dst, int n_threads,
+                                int* all_exact);
+
 #ifdef __cplusplus
 }
 #endif

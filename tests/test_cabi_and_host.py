@@ -144,3 +144,26 @@ def test_bench_reference_arm_prints_one_json_line():
     env2 = dict(env, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
     res2 = subprocess.run(cmd, capture_output=True, text=True, env=env2, timeout=600)
     assert res2.returncode == 0 and res2.stdout.strip() == "", (res2.returncode, res2.stdout, res2.stderr[-500:])
+
+
+def test_host_pack_recovers_png_codes_exactly():
+    """rac_host_pack_gt_u8 (host-only staging, csrc/host_pack.cu): real.png / 255.0 (image_dataloaders.py:79-83) -> the
+    PNG's codes, accepted only when EVERY value is exactly q / 255.0; ragged sizes, both source types, thread counts."""
+    import ctypes
+    from rac import _lib
+    L = _lib.lib()
+    rng = np.random.default_rng(0)
+    ok = ctypes.c_int(-1)
+    for n in (1, 63, 64, 65, 70001, 3 * 320 * 240 * 5 + 7):
+        q = rng.integers(0, 256, n, dtype=np.uint8)
+        for src, is64 in ((q / 255.0, 1), ((q / 255.0).astype(np.float32), 0)):
+            for nt in (1, 3, 0):
+                dst = np.full(n, 7, np.uint8)
+                assert L.rac_host_pack_gt_u8(src.ctypes.data, is64, n, dst.ctypes.data, nt, ctypes.byref(ok)) == 0
+                assert ok.value == 1 and (dst == q).all()
+        for bad in (np.nextafter(0.5, 1.0), -1.0 / 255.0, 256.0 / 255.0, np.nan, np.inf, 0.3):
+            src = q / 255.0
+            src[n // 2] = bad
+            assert L.rac_host_pack_gt_u8(src.ctypes.data, 1, n, dst.ctypes.data, 0, ctypes.byref(ok)) == 0
+            assert ok.value == 0, (n, bad)
+    assert L.rac_host_pack_gt_u8(None, 1, 4, dst.ctypes.data, 0, ctypes.byref(ok)) < 0

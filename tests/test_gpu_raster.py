@@ -299,30 +299,108 @@ def test_assemble_input_pinned_gt_overlapped_upload(rac, B, use_depth):
 
 
 def test_gt_cache_across_refinement_iterations(rac):
-    """The same torch gt tensor passed again (the reference's `for j` loop, train_model.py:234-250) reuses the
-    normalised planes left on the device; an in-place change or a different tensor does not."""
+    """The same gt crop passed again (the reference's `for j` loop, train_model.py:234-250) reuses the normalised planes
+    left on the device.  Host arrays — numpy, as the drivers pass them (train_model.py:226), and CPU tensors — are
+    recognised by address + a content fingerprint, so a buffer REFILLED behind torch's back (through a numpy view: no
+    version bump) misses instead of handing back the previous batch's planes."""
     from rac import render as R
     rng = np.random.default_rng(21)
     B, H, W = 8, 48, 64
     mk = lambda: torch.tensor(rng.uniform(0, 1, (B, H, W, 3)).astype(np.float32), device="cuda")
+    codes = lambda: rng.integers(0, 256, (B, H, W, 3))
     init1, init2 = mk(), mk()
-    gt = torch.tensor((rng.integers(0, 256, (B, H, W, 3)) / 255.0).astype(np.float32)).pin_memory()
     prev = R.set_gt_cache(True)
     try:
-        x1 = rac.assemble_input_device(init1, gt, None, False)
-        assert R._gt_cache_lookup(gt, x1.device) is not None
-        x2 = rac.assemble_input_device(init2, gt, None, False)            # hit: gt planes come from the cache
-        ref2 = assemble_ref.prepare_model_input(init2.cpu().numpy(), gt.numpy().astype(np.float64), None, False).numpy()
-        assert torch.equal(x1[:, 3:], x2[:, 3:])
-        np.testing.assert_allclose(x2.cpu().numpy(), ref2, rtol=1e-5, atol=2e-5)
-        gt.mul_(0.5)                                                      # in-place change -> version bump -> miss
-        assert R._gt_cache_lookup(gt, x1.device) is None
-        x3 = rac.assemble_input_device(init2, gt, None, False)
-        ref3 = assemble_ref.prepare_model_input(init2.cpu().numpy(), gt.numpy().astype(np.float64), None, False).numpy()
-        np.testing.assert_allclose(x3.cpu().numpy(), ref3, rtol=1e-5, atol=2e-5)
-        assert R._gt_cache_lookup(gt.numpy(), x1.device) is None          # numpy arrays are never cached
+        for form in ("numpy_f64", "pinned_f32"):
+            R.set_gt_cache(False); R.set_gt_cache(True)          # start empty
+            g0 = codes() / 255.0
+            gt = g0.copy() if form == "numpy_f64" else torch.tensor(g0.astype(np.float32)).pin_memory()
+            as64 = lambda t: (t if isinstance(t, np.ndarray) else t.numpy()).astype(np.float64)
+            x1 = rac.assemble_input_device(init1, gt, None, False)
+            assert R._gt_cache_lookup(gt, x1.device) is not None, form
+            x2 = rac.assemble_input_device(init2, gt, None, False)            # hit: gt planes come from the cache
+            assert torch.equal(x1[:, 3:], x2[:, 3:])
+            np.testing.assert_allclose(x2.cpu().numpy(), assemble_ref.prepare_model_input(init2.cpu().numpy(), as64(gt), None, False).numpy(),
+                                       rtol=1e-5, atol=2e-5)
+            # the buffer is refilled with the next batch through a numpy view (what a loader that recycles a staging
+            # tensor does): same object, same address, same torch version counter — different content
+            view = gt if isinstance(gt, np.ndarray) else gt.numpy()
+            view[...] = (codes() / 255.0).astype(view.dtype)
+            assert R._gt_cache_lookup(gt, x1.device) is None, form
+            x3 = rac.assemble_input_device(init2, gt, None, False)
+            np.testing.assert_allclose(x3.cpu().numpy(), assemble_ref.prepare_model_input(init2.cpu().numpy(), as64(gt), None, False).numpy(),
+                                       rtol=1e-5, atol=2e-5)
+            assert not torch.equal(x3[:, 3:], x2[:, 3:])
+            # one image of the batch replaced: the strided fingerprint covers every image
+            view[B - 1] = (rng.integers(0, 256, (H, W, 3)) / 255.0).astype(view.dtype)
+            assert R._gt_cache_lookup(gt, x1.device) is None, form
+        # CUDA tensors: identity + version counter
+        gd = torch.tensor((codes() / 255.0).astype(np.float32), device="cuda")
+        rac.assemble_input_device(init1, gd, None, False)
+        assert R._gt_cache_lookup(gd, gd.device) is not None
+        gd.mul_(0.5)
+        assert R._gt_cache_lookup(gd, gd.device) is None
         R.set_gt_cache(False)
         assert R._gt_cache_lookup(gt, x1.device) is None
+    finally:
+        R.set_gt_cache(prev)
+
+
+@pytest.mark.parametrize("use_depth", [False, True])
+def test_unchanged_loader_crop_travels_as_bytes(rac, use_depth):
+    """The crop the unchanged loader produces — real.png / 255.0, float64, pageable numpy (image_dataloaders.py:79-83) —
+    is packed to its PNG codes on the way into pinned staging (rac_host_pack_gt_u8) and normalised by rac_gt_norm_u8:
+    the planes must be BIT-identical to handing over the uint8 codes, and equal to the reference's f64 arithmetic cast
+    to f32.  A float crop that is not made of exact codes takes the float path (1e-5)."""
+    from rac import render as R
+    rng = np.random.default_rng(33)
+    B, H, W = 9, 40, 56
+    init = torch.tensor(rng.uniform(0, 1, (B, H, W, 3)).astype(np.float32), device="cuda")
+    depth = torch.tensor(np.where(rng.uniform(size=(B, H, W)) > 0.5, rng.uniform(2.2, 2.8, (B, H, W)), 0).astype(np.float32), device="cuda")
+    prev = R.set_gt_cache(False)
+    try:
+        for rep in range(4):             # > ring depth: the pinned staging slots are reused
+            q = rng.integers(0, 256, (B, H, W, 3), dtype=np.uint8)
+            g64 = q / 255.0
+            assert g64.dtype == np.float64
+            x_f64 = rac.assemble_input_device(init, g64, depth, use_depth)
+            x_u8 = rac.assemble_input_device(init, q, depth, use_depth)
+            assert torch.equal(x_f64, x_u8), rep
+            ref = assemble_ref.prepare_model_input(init.cpu().numpy(), g64, depth.cpu().numpy(), use_depth).numpy()
+            c0 = 4 if use_depth else 3
+            got = x_f64.cpu().numpy()
+            assert (got[:, c0:] == ref[:, c0:]).mean() > 0.9999
+            np.testing.assert_allclose(got, ref, rtol=1e-5, atol=2e-5)
+        g = rng.uniform(0, 1, (B, H, W, 3))                     # not PNG codes: float path
+        x = rac.assemble_input_device(init, g, depth, use_depth).cpu().numpy()
+        ref = assemble_ref.prepare_model_input(init.cpu().numpy(), g, depth.cpu().numpy(), use_depth).numpy()
+        np.testing.assert_allclose(x, ref, rtol=1e-5, atol=2e-5)
+        g = q / 255.0
+        g[B - 1, H - 1, W - 1, 2] = np.nextafter(g[B - 1, H - 1, W - 1, 2], 2.0)      # ONE value one ulp off a code
+        x = rac.assemble_input_device(init, g, depth, use_depth).cpu().numpy()
+        np.testing.assert_allclose(x, assemble_ref.prepare_model_input(init.cpu().numpy(), g, depth.cpu().numpy(), use_depth).numpy(),
+                                   rtol=1e-5, atol=2e-5)
+    finally:
+        R.set_gt_cache(prev)
+
+
+def test_pinned_caller_buffer_may_be_refilled_after_return(rac):
+    """prepare_model_input is synchronous in the reference: a caller that recycles its (pinned) gt buffer right after the
+    call must not race with the library's asynchronous upload."""
+    from rac import render as R
+    rng = np.random.default_rng(8)
+    B, H, W = 64, 120, 160
+    init = torch.tensor(rng.uniform(0, 1, (B, H, W, 3)).astype(np.float32), device="cuda")
+    gt = torch.empty((B, H, W, 3), dtype=torch.float32).pin_memory()
+    prev = R.set_gt_cache(False)
+    try:
+        for rep in range(3):
+            g = rng.uniform(0, 1, (B, H, W, 3)).astype(np.float32)
+            gt.numpy()[...] = g
+            x = rac.assemble_input_device(init, gt, None, False)
+            gt.numpy()[...] = -1.0                     # refill immediately, no synchronisation by the caller
+            ref = assemble_ref.prepare_model_input(init.cpu().numpy(), g.astype(np.float64), None, False).numpy()
+            np.testing.assert_allclose(x.cpu().numpy(), ref, rtol=1e-5, atol=2e-5)
     finally:
         R.set_gt_cache(prev)
 
