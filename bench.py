@@ -13,9 +13,17 @@ one synthetic ModelNet10-scale untextured mesh of ~10k triangles, 6D head, N=100
 For N>1 launch with torch.distributed.run (the driver does); weak scaling: every rank renders its own
 64 poses, the only collective is the scalar loss all-reduce (NCCL).
 
-`value`   = renders/s with inputs resident in HBM (device-timed, CUDA events on the launching stream).
-`e2e`     = the same through the reference-facing Python API (data_loaders.render_batch /
-            prepare_model_input / calculate_T_CO_pred / loss) with HOST (pinned) buffers in, host pose out.
+`value`   = renders/s with inputs resident in HBM (device-timed, CUDA events on the launching stream), for the loop's
+            true SERIAL chain: render -> pose update + loss + backward -> T_pred <- T_new, one CUDA-graph replay per
+            iteration (rac.RenderCompareStep.run_chain); `value_overlapped` is the upper bound with pose/loss on a parallel
+            graph branch, `iters_per_sec_with_cnn` the same chain with a stock-PyTorch BaseNet-shaped CNN in the loop
+            (forward + backward + Adam step, eager).
+`e2e`     = the same through the reference-facing Python API in the call sequence of test_model.validate_model /
+            train_model.train (render_batch -> torch.tensor(T) -> prepare_model_input -> calculate_T_CO_pred -> loss ->
+            backward -> .cpu().numpy()), with the input TYPES the unchanged drivers pass: gt crop = pageable float64
+            numpy (image_dataloaders.py:79-83), cam_mats = float64 CPU tensor, mesh paths = strings; batches of 3
+            refinement iterations, a different gt array every batch.  Secondary figures: a fresh gt crop in EVERY
+            iteration (`e2e_fresh_gt`), pinned float32 crops (`e2e_pinned_f32`, round 1's arm) and uint8 crops (`e2e_u8`).
 `roofline`= the rasterize+concat stage (setup + raster + gt_norm + finalize_live kernels of one rac_render_concat call),
             algorithmic bytes 36*W*H per image over its CUDA-event time.
 `--impl reference` times the CPU oracle (oracle/: C rasteriser restatement + reference-restated torch CPU
@@ -158,6 +166,7 @@ def run_ours(args):
     M.save_ply(ply, mesh)
     mesh_paths = [ply] * B
     Ks_cpu = torch.tensor(K)                      # stays on the CPU like the reference's cam_mats (Q5)
+    Ks_f64 = torch.tensor(K.astype(np.float64))   # K.npy is float64 on disk: what the drivers' cam_mats really is
     Kd = Ks_cpu.to(dev)
 
     # gt crops: our own render at T_gt + U(0,8)/255 noise, quantised to u8
@@ -172,6 +181,11 @@ def run_ours(args):
         # pinned host copies for the e2e arm
         d["h_gt"] = gt.cpu().pin_memory()
         d["h_gt_u8"] = torch.round(gt * 255.0).to(torch.uint8).cpu().pin_memory()      # the same crop as 8-bit codes
+        # what the unchanged loader hands over (image_dataloaders.py:79-83): real.png / 255.0 -> float64, pageable numpy
+        d["np_gt_f64"] = d["h_gt_u8"].numpy().astype(np.float64) / 255.0
+        d["T_init_f64"] = torch.tensor(s["T_init"].astype(np.float64))                 # T_CO_init.npy is float64
+        d["cpu_T_gt"] = torch.tensor(s["T_gt"])
+        d["cpu_pts"] = torch.tensor(s["pts"])
         d["h_T_init"] = torch.tensor(s["T_init"]).pin_memory()
         d["h_T_gt"] = torch.tensor(s["T_gt"]).pin_memory()
         d["h_y"] = torch.tensor(s["y"]).pin_memory()
@@ -186,16 +200,25 @@ def run_ours(args):
         st.capture()
         steps_obj.append(st)
         d["gt"] = st.gt            # the e2e arm and the checks below reuse the step's buffers
-    launches_per_step = steps_obj[0].launches_per_run
+    launches_per_step = steps_obj[0].launches_per_chain
+    ITERS_PER_BATCH = 3      # BASELINE configs[1]: "batch 64, 3 refinement iters"
 
     pending = [None] * NSETS
 
-    def step_device(i):
+    def step_device(i, chain=True):
+        """One refinement iteration.  chain: the serial dependency chain of the real loop (render -> pose/loss ->
+        T_pred <- T_new); every ITERS_PER_BATCH-th visit of a buffer set starts a new batch from T_init, as the loop
+        does (train_model.py:233), so the poses stay in the sampled range however many steps are timed."""
         k = i % NSETS
         st = steps_obj[k]
         if pending[k] is not None:
             pending[k].wait()                     # stream-side wait: this set's previous loss reduction has finished
-        st.run()
+        if chain:
+            if (i // NSETS) % ITERS_PER_BATCH == 0:
+                st.T_pred.copy_(dsets[k]["T_init"])
+            st.run_chain()
+        else:
+            st.run()
         if world > 1:
             # the logged loss mean (SURVEY.md §8e): one scalar all-reduce per step, issued asynchronously so that its
             # latency (NCCL launch + NVLink round trip, ~25 us at 8 GPUs) overlaps the next step's rasteriser
@@ -228,15 +251,40 @@ def run_ours(args):
         torch.cuda.current_stream().synchronize()
         return x
 
-    ITERS_PER_BATCH = 3      # BASELINE configs[1]: "batch 64, 3 refinement iters"
+    def step_e2e_driver(i, fresh_gt=False):
+        """One drawn batch as the unchanged drivers run it (train_model.py:222-250 / test_model.py:86-108), with the
+        drivers' own input TYPES: gt_imgs = pageable float64 numpy, cam_mats = float64 CPU tensor, T_CO_init float64,
+        mesh_paths = strings.  ITERS_PER_BATCH refinement iterations: render under the current pose, assemble the
+        input with the SAME gt_imgs object, pose update, loss, backward, pose back to numpy.  The shadow
+        prepare_model_input packs the crop to its PNG codes on its first sight (one threaded pass + 3 B/px upload) and
+        recognises it in the later iterations.  fresh_gt: hand over a DIFFERENT gt array in every iteration (worst
+        case: every iteration pays the pack + upload)."""
+        s = dsets[i % NSETS]
+        gt_imgs = s["np_gt_f64"]
+        T_pred = s["T_init_f64"]
+        T_gt = s["cpu_T_gt"].to(dev)                                                           # :228
+        pts = s["cpu_pts"].to(dev)                                                             # :229
+        for j in range(ITERS_PER_BATCH):
+            if fresh_gt:
+                gt_imgs = dsets[(i * ITERS_PER_BATCH + j) % NSETS]["np_gt_f64"]
+            imgs, depths = DL.render_batch(T_pred if j else T_pred.numpy(), mesh_paths, Ks_f64, (W, H), False)   # :240
+            T_dev = torch.tensor(T_pred).to(dev) if j else T_pred.to(dev)                      # :241 / :238 (f64 at j == 0, Q6)
+            x = DL.prepare_model_input(imgs, gt_imgs, depths, False).to(dev)                   # :243
+            y = s["h_y"].to(dev, non_blocking=True).requires_grad_(True)                       # (CNN output stand-in)
+            T_new = RR.calculate_T_CO_pred(y, T_dev, ROT, Ks_f64)                              # :245
+            l = L.compute_disentangled_ADD_L1_loss(T_gt, T_new, pts)                           # :247 / :280
+            l.backward()
+            if world > 1:
+                lb = l.detach().reshape(1).clone()
+                dist.all_reduce(lb)
+            T_pred = T_new.detach().cpu().numpy()                                              # :250 (synchronises)
+            h_loss_out.copy_(l.detach().reshape(1))                                            # :254 (.item())
+        return x
 
     def step_e2e_batch(i):
-        """One batch as the reference's loop runs it (train_model.py:224-250): the gt crop is drawn once, then
-        ITERS_PER_BATCH refinement iterations render under the updated pose and re-assemble the input with the SAME
-        gt_imgs object — the shadow prepare_model_input recognises it (torch version counter) and reuses the
-        normalised planes it left on the device instead of uploading and normalising again."""
+        """Round 1's secondary figure: the same loop shape on pinned float32 torch crops."""
         s = dsets[i % NSETS]
-        s["h_gt"][0, 0, 0, 0:1].add_(0)            # a fresh batch: bump the tensor's version so nothing cached matches
+        s["h_gt"][0, 0, 0, 0:1].add_(0)
         T_pred = s["h_T_init"].numpy()
         T_gt = s["h_T_gt"].to(dev, non_blocking=True)
         pts = s["h_pts"].to(dev, non_blocking=True)
@@ -253,6 +301,44 @@ def run_ours(args):
             torch.cuda.current_stream().synchronize()
             T_pred = h_pose_out.numpy().copy()
         return x
+
+    # ---- the stock CNN in the loop (secondary): a BaseNet-shaped stand-in (models/baseline_net.py:5-34: five blocks
+    # of conv-bn-relu x2 + maxpool, 32-48-64-64-32 channels, one Linear), last layer sized for this resolution.  Stock
+    # PyTorch, random init, training mode: forward, backward from grad_y, Adam step — the part of an iteration that
+    # is NOT this repo's, timed with it so that iterations/s of the whole loop can be quoted.
+    def make_cnn():
+        import torch.nn as nn
+
+        def block(ci, co):
+            return nn.Sequential(nn.Conv2d(ci, co, 3, 1, 1), nn.BatchNorm2d(co), nn.ReLU(),
+                                 nn.Conv2d(co, co, 3, 1, 1), nn.BatchNorm2d(co), nn.ReLU(), nn.MaxPool2d(2, 2))
+        chans = [6, 32, 48, 64, 64, 32]
+        body = nn.Sequential(*[block(chans[k], chans[k + 1]) for k in range(5)], nn.Flatten())
+        return nn.Sequential(body, nn.Linear(32 * (H // 32) * (W // 32), 9)).to(dev)
+
+    cnn_state = {}
+
+    def step_with_cnn(i):
+        if not cnn_state:
+            torch.manual_seed(0)
+            cnn_state["net"] = make_cnn()
+            cnn_state["opt"] = torch.optim.Adam(cnn_state["net"].parameters(), lr=3e-4)
+        net, opt = cnn_state["net"], cnn_state["opt"]
+        k = i % NSETS
+        st = steps_obj[k]
+        if (i // NSETS) % ITERS_PER_BATCH == 0:
+            st.T_pred.copy_(dsets[k]["T_init"])
+        opt.zero_grad(set_to_none=True)
+        st.run_render()                                     # x <- render(T_pred) ++ gt
+        out = net(st.x)                                     # stock CNN
+        # the (untrained) head output is squashed into the range a trained head produces, so that the poses stay in view
+        y = torch.cat([out[:, :6] * 0.05, out[:, 6:8] * 0.01, 1.0 + 0.01 * torch.tanh(out[:, 8:9])], 1)
+        y = y + torch.tensor([1, 0, 0, 0, 1, 0, 0, 0, 0], device=dev, dtype=torch.float32)
+        st.y.copy_(y.detach())
+        st.run_pose_loss()                                  # T_new, loss, grad_y
+        y.backward(st.grad_y)
+        opt.step()
+        st.T_pred.copy_(st.T_new)
 
     def barrier():
         if world > 1:
@@ -282,26 +368,50 @@ def run_ours(args):
     ms, wall_ms = timed(step_device, args.steps)
     launches = launches_per_step * args.steps
     clocks = sampler.result()
+    # upper bound: pose / loss on a parallel graph branch under the rasteriser (round 1's `value`)
+    step_overlapped = lambda i: step_device(i, chain=False)
+    for i in range(3):
+        step_overlapped(i)
+    ov_ms, _ = timed(step_overlapped, args.steps)
     # the rasterize+concat stage on its own (same graphs, render part only) for the roofline line
     for i in range(3):
         step_render_only(i)
     stage_total_ms, _ = timed(step_render_only, args.steps)
     stage_ms = stage_total_ms / args.steps
+    # the chain with the stock CNN in the loop
+    cnn_steps = max(6, min(args.steps, 24))
+    for i in range(3):
+        step_with_cnn(i)
+    cnn_ms, _ = timed(step_with_cnn, cnn_steps)
+    cnn_state.clear()
+    torch.cuda.empty_cache()
 
     from rac import render as _render
-    _render.set_gt_cache(False)      # the per-step end-to-end figure: every step uploads and normalises its own gt crop
+    e2e_sync = lambda: torch.cuda.synchronize()
+    # headline e2e: the drivers' loop shape and input types
+    _render.set_gt_cache(True)
+    nb_batches = max(args.steps // ITERS_PER_BATCH, 4)
+    for i in range(3):
+        step_e2e_driver(i)
+    ed_ms, ed_wall_ms = timed(step_e2e_driver, nb_batches)
+    ed_ms = max(ed_ms, ed_wall_ms)   # e2e includes host work: take the larger of device and wall clocks
+    step_e2e_fresh = lambda i: step_e2e_driver(i, fresh_gt=True)
+    for i in range(2):
+        step_e2e_fresh(i)
+    ef_ms, ef_wall_ms = timed(step_e2e_fresh, nb_batches)
+    ef_ms = max(ef_ms, ef_wall_ms)
+    _render.set_gt_cache(False)      # secondary (round 1's arm): per-step calls on pinned float32 crops, every step uploads
     for i in range(max(args.warmup, 3)):
         step_e2e(i)
     e_ms, e_wall_ms = timed(step_e2e, args.steps)
-    e_ms = max(e_ms, e_wall_ms)      # e2e includes host work: take the larger of device and wall clocks
+    e_ms = max(e_ms, e_wall_ms)
     # secondary figure: the same step with the gt crop handed over as the PNG's 8-bit codes (rac_gt_norm_u8)
     step_e2e_u8 = lambda i: step_e2e(i, "h_gt_u8")
     for i in range(max(args.warmup, 3)):
         step_e2e_u8(i)
     eu_ms, eu_wall_ms = timed(step_e2e_u8, args.steps)
     eu_ms = max(eu_ms, eu_wall_ms)
-    _render.set_gt_cache(True)       # secondary figure: whole batches of ITERS_PER_BATCH iterations, gt uploaded once per batch
-    nb_batches = max(args.steps // ITERS_PER_BATCH, 4)
+    _render.set_gt_cache(True)       # secondary figure: whole batches of ITERS_PER_BATCH iterations on pinned f32 crops
     for i in range(3):
         step_e2e_batch(i)
     eb_ms, eb_wall_ms = timed(step_e2e_batch, nb_batches)
@@ -317,41 +427,76 @@ def run_ours(args):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    traffic = None       # DRAM bytes per rac_render_concat call, from the committed ncu capture of this same command
+    # DRAM bytes per rac_render_concat call from the committed ncu capture of this same command — valid only for the
+    # kernels it was taken on: the capture records the digest of the library sources (build.py's stamp), and the field
+    # is null when the library in use was built from different sources.
+    traffic, traffic_rev, traffic_note = None, None, "no capture committed"
+    lib_digest = None
     try:
-        with open(os.path.join(ROOT, "profiles", "traffic_r01.json")) as f:
-            traffic = float(json.load(f)["stage_dram_bytes_per_call"])
+        with open(os.path.join(PKG, ".librac_b200.stamp")) as f:
+            lib_digest = f.read().strip()[:16]
+    except Exception:
+        pass
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic_r02.json")) as f:
+            tj = json.load(f)
+        traffic_rev = tj.get("lib_digest")
+        if traffic_rev and lib_digest and traffic_rev == lib_digest:
+            traffic = float(tj["stage_dram_bytes_per_call"])
+            traffic_note = ("profiles/traffic_r02.json: ncu dram__bytes_read+write summed over the stage's kernels, per call "
+                            "(serialised capture, so part of the 118 MB written is still dirty in the 126 MB L2 when the last kernel ends)")
+        else:
+            traffic_note = "profiles/traffic_r02.json was captured on library sources %s, this run uses %s: stale, not reported" % (traffic_rev, lib_digest)
     except Exception:
         pass
     achieved = algo_bytes / (stage_ms * 1e-3) / 1e9
-    h2d = sum(dsets[0][k].numel() * 4 for k in ("h_gt", "h_T_init", "h_T_gt", "h_y", "h_pts"))
+    small_h2d = sum(dsets[0][k].numel() * 4 for k in ("h_T_init", "h_T_gt", "h_y", "h_pts"))
+    h2d = small_h2d + dsets[0]["h_gt"].numel() * 4
+    gt_codes = dsets[0]["h_gt_u8"].numel()            # bytes the packed crop puts on PCIe
+    drv_iters = ITERS_PER_BATCH * nb_batches
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "iters_per_sec": world * args.steps / (ms * 1e-3),
+        "value_note": "serial chain per iteration: render -> pose update + loss + backward -> T_pred <- T_new (one graph replay); a new batch (T_init) every %d iterations" % ITERS_PER_BATCH,
+        "value_overlapped": world * B * args.steps / (ov_ms * 1e-3),
+        "iters_per_sec_overlapped": world * args.steps / (ov_ms * 1e-3),
+        "iters_per_sec_with_cnn": world * cnn_steps / (cnn_ms * 1e-3),
+        "with_cnn": {"ms_per_iter": cnn_ms / cnn_steps, "renders_per_s": world * B * cnn_steps / (cnn_ms * 1e-3), "iters": cnn_steps,
+                     "cnn": "BaseNet-shaped stand-in (models/baseline_net.py:5-34; last Linear sized for %dx%d), stock PyTorch eager, f32: forward + backward + Adam step between the render graph and the pose/loss graph" % (W, H)},
         "config": {"workload": workload_name(), "global_batch": world * B, "width": W, "height": H, "triangles": len(mesh.faces),
                    "rot_repr": ROT, "loss": LOSS, "points": NPTS, "parallelism": "dp%d (batch sharded, no data-path collective)" % world,
                    "l2": "rotating %d input/output sets (%.0f MB each) > 126 MB L2" % (NSETS, (36.0 * W * H * B) / 1e6)},
         "roofline": {"bound": "hbm", "kernel": "rac_render_concat stage (setup + raster + finalize_live kernels, gt_norm on a forked stream under them), timed as its own graph replay",
                      "achieved": achieved, "peak": peak, "peak_source": "measured" if peaks else "fallback",
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "traffic_source": "profiles/traffic_r01.json: ncu dram__bytes_read+write summed over the stage's 4 kernels, per call (serialised, so part of the 118 MB written is still dirty in the 126 MB L2 when the last kernel ends)",
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_rev": traffic_rev, "lib_digest": lib_digest,
+                     "traffic_source": traffic_note,
                      "stage_ms": stage_ms, "algorithmic_bytes": algo_bytes,
                      "triangle_setup_rate_per_s": B * len(mesh.faces) / (stage_ms * 1e-3)},
-        "e2e": {"value": world * B * args.steps / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms / args.steps,
-                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 64 + 4,
-                "api": "data_loaders.render_batch_sequential + prepare_model_input + calculate_T_CO_pred + compute_disentangled_ADD_L1_loss + backward"},
+        "e2e": {"value": world * B * drv_iters / (ed_ms * 1e-3), "unit": UNIT, "ms_per_step": ed_ms / drv_iters,
+                "h2d_bytes_per_step": (gt_codes + small_h2d) // ITERS_PER_BATCH + B * 128 + B * 36, "d2h_bytes_per_step": B * 64 + 4,
+                "host_bytes_read_per_step": dsets[0]["np_gt_f64"].nbytes // ITERS_PER_BATCH,
+                "iters_per_batch": ITERS_PER_BATCH, "batches": nb_batches,
+                "api": "validate_model / train call sequence (test_model.py:95-108, train_model.py:236-250): data_loaders.render_batch -> torch.tensor(T_CO_pred).to(device) -> "
+                       "prepare_model_input(pred_imgs, gt_imgs, depths) -> calculate_T_CO_pred(y, T, '6D', cam_mats) -> compute_disentangled_ADD_L1_loss -> backward -> .cpu().numpy()",
+                "input_types": "gt_imgs: numpy float64 pageable (B,H,W,3) = real.png / 255.0; cam_mats: torch float64 CPU; T_CO_init: torch float64 CPU; mesh_paths: list of str; "
+                               "a different gt array every batch (the cache holds 2, the bench rotates %d)" % NSETS},
+        "e2e_fresh_gt": {"value": world * B * drv_iters / (ef_ms * 1e-3), "unit": UNIT, "ms_per_step": ef_ms / drv_iters,
+                         "h2d_bytes_per_step": gt_codes + small_h2d // ITERS_PER_BATCH + B * 128 + B * 36, "d2h_bytes_per_step": B * 64 + 4,
+                         "host_bytes_read_per_step": dsets[0]["np_gt_f64"].nbytes,
+                         "note": "secondary, worst case: the same loop with a DIFFERENT float64 numpy gt array in every iteration (every iteration reads 118 MB of "
+                                 "host memory to pack the crop and uploads it)"},
+        "e2e_pinned_f32": {"value": world * B * args.steps / (e_ms * 1e-3), "unit": UNIT, "ms_per_step": e_ms / args.steps,
+                           "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": B * 64 + 4,
+                           "note": "secondary (round 1's e2e arm): per-step calls with a PINNED float32 torch crop, uploaded and normalised every step"},
         "e2e_u8": {"value": world * B * args.steps / (eu_ms * 1e-3), "unit": UNIT, "ms_per_step": eu_ms / args.steps,
                    "h2d_bytes_per_step": h2d - 3 * dsets[0]["h_gt"].numel(), "d2h_bytes_per_step": B * 64 + 4,
-                   "note": "secondary: the same per-step calls with the gt crop handed to prepare_model_input as uint8 (the PNG's codes; the "
-                           "loader's `/ 255.0`, image_dataloaders.py:79-83, moves into rac_gt_norm_u8) — 3 B/px over PCIe instead of 12, planes "
-                           "bit-identical to the reference's f64 -> f32 cast"},
+                   "note": "secondary: per-step calls with the gt crop handed to prepare_model_input as pinned uint8 (the PNG's codes), every step uploads"},
         "e2e_batch": {"value": world * B * ITERS_PER_BATCH * nb_batches / (eb_ms * 1e-3), "unit": UNIT,
                       "ms_per_batch": eb_ms / nb_batches, "iters_per_batch": ITERS_PER_BATCH, "batches": nb_batches,
                       "h2d_bytes_per_batch": h2d + (ITERS_PER_BATCH - 1) * (B * 64 + B * 9 * 4), "d2h_bytes_per_batch": ITERS_PER_BATCH * (B * 64 + 4),
-                      "note": "secondary: the reference's loop shape (configs[1]: 3 refinement iterations per drawn batch, same gt_imgs "
-                              "object every iteration) — the gt crop is uploaded and normalised once per batch; `e2e` above pays it every step"},
+                      "note": "secondary (round 1): the loop shape on pinned float32 crops, gt uploaded and normalised once per batch"},
         "gpu_launches": int(launches), "clocks": clocks,
     }
     if rank == 0:

@@ -198,8 +198,8 @@ def _assemble_call(L, init, gt, d, B, W, H, use_norm_depth, x, dev):
 # planes of the last few crops stay on the device and later iterations skip the upload and the normalisation
 # (SURVEY.md §8f N1).  What identifies "the same crop":
 #   host arrays (numpy — what the drivers pass, train_model.py:226 — and CPU tensors): address, shape, dtype, strides
-#       AND a content fingerprint taken at insert and at lookup — the raw bytes of ~8 k values strided across the whole
-#       array (>= 128 per image at batch 64) plus its first and last 256 values.  A buffer refilled with another batch
+#       AND a content fingerprint taken at insert and at lookup — the raw bytes of ~2 k values strided across the whole
+#       array (32 per image at batch 64; every sample is a cache miss in pageable memory, ~80 ns each) plus its first and last 256 values.  A buffer refilled with another batch
 #       (through a numpy view, from_numpy-shared storage, in place, ...) differs in the fingerprint and misses; torch's
 #       version counter is NOT consulted (it does not see writes through numpy views);
 #   CUDA tensors: object identity, storage pointer and in-place version counter (no host copy of a fingerprint
@@ -208,7 +208,7 @@ def _assemble_call(L, init, gt, d, B, W, H, use_norm_depth, x, dev):
 _gt_cache = []          # [dict(key, fp | ref+version, dev, planes (B,3,H,W))], most recent last
 _GT_CACHE_ENTRIES = 2
 _gt_cache_enabled = True
-_FP_STRIDED = 8192
+_FP_STRIDED = 2048
 _FP_EDGE = 256
 
 

@@ -11,6 +11,15 @@ device buffers and replays a captured graph:
 
 `step.x` is what the CNN consumes; `step.grad_y` is dLoss/d(cnn output), to be fed to `cnn_out.backward(grad_y)`.
 A caller that wants the CNN between render and pose update uses run_render() / run_pose_loss() (two graphs).
+
+Three replayable forms of the iteration:
+    run_chain()  the loop's true dependency chain (train_model.py:240-250): render -> pose update + loss + backward ->
+                 T_pred <- T_new, strictly in that order on one stream — in the real loop y = CNN(x), so the pose / loss
+                 kernels can never start before the render of the same iteration has finished, and the next render
+                 needs the updated pose.  This is the figure bench.py reports as `value`;
+    run()        render and pose/loss as two parallel graph branches (legal only while y does not depend on x: an upper
+                 bound, reported as `value_overlapped`); T_pred is left alone;
+    run_render() / run_pose_loss()   the two halves, for a caller that runs its CNN in between.
 Kernels only — the captured work is exactly the C-ABI calls of include/rac.h (no CPU fallback).
 """
 import torch
@@ -49,7 +58,7 @@ class RenderCompareStep:
         self.grad_y = torch.zeros((B, D), **f32)
         self._fx, self._fy = fx, fy
         self._L, self._RR = L, RR
-        self._g_all = self._g_render = self._g_pose = None
+        self._g_all = self._g_render = self._g_pose = self._g_chain = None
 
     # ---- the eager bodies (also what gets captured) ----
     def _render(self):
@@ -109,12 +118,25 @@ class RenderCompareStep:
             self._render()
             main.wait_stream(s)
         self.launches_per_run = _lib.launch_count() - n0     # librac kernels replayed by every run()
+        self._g_chain = torch.cuda.CUDAGraph()
+        n0 = _lib.launch_count()
+        with torch.cuda.graph(self._g_chain):
+            self._render()
+            self._pose_loss()
+            self.T_pred.copy_(self.T_new)                    # train_model.py:250: the next iteration renders under T_new
+            self.T_prev.copy_(self.T_new)                    # (the scaled loss reads the iteration's input pose, train_model.py:283)
+        self.launches_per_chain = _lib.launch_count() - n0
         return self
 
     def run(self):
         if self._g_all is None:
             self.capture()
         self._g_all.replay()
+
+    def run_chain(self):
+        if self._g_chain is None:
+            self.capture()
+        self._g_chain.replay()
 
     def run_render(self):
         if self._g_render is None:
