@@ -112,14 +112,24 @@ int rac_device_info(int* sm_count, int* cc_major, int* cc_minor) {
     return RAC_OK;
 }
 
-int rac_mesh_create(const float* h_verts, int V, const int32_t* h_faces, int T,
-                    const float* h_uv, const uint8_t* h_tex, int tw, int th,
-                    const uint8_t* h_vcolor, const rac_material_t* mat, rac_mesh_t* out) {
+// Shared body of rac_mesh_create / rac_mesh_create_parts.  n_parts == 0: single material `mat`, texture h_tex.
+static int mesh_create_common(const float* h_verts, int V, const int32_t* h_faces, int T,
+                              const float* h_uv, const uint8_t* h_tex, int tw, int th,
+                              const uint8_t* h_vcolor, const rac_material_t* mat,
+                              const uint8_t* h_face_part, int n_parts, const rac_part_t* parts, rac_mesh_t* out) {
     RAC_REQUIRE(h_verts && h_faces && out, "rac_mesh_create: null verts/faces/out");
     RAC_REQUIRE(V > 0 && T > 0, "rac_mesh_create: V=%d T=%d must be positive", V, T);
     RAC_REQUIRE(!h_tex || (h_uv && tw > 0 && th > 0), "rac_mesh_create: texture needs uv and tw,th>0");
     for (int i = 0; i < 3 * T; ++i)
         RAC_REQUIRE(h_faces[i] >= 0 && h_faces[i] < V, "rac_mesh_create: face index %d out of range", h_faces[i]);
+    if (n_parts > 0) {
+        RAC_REQUIRE(h_face_part && parts && n_parts <= 255, "rac_mesh_create_parts: needs face_part, parts, n_parts <= 255");
+        for (int t = 0; t < T; ++t)
+            RAC_REQUIRE(h_face_part[t] < n_parts, "rac_mesh_create_parts: face %d names part %d of %d", t, (int)h_face_part[t], n_parts);
+        for (int k = 0; k < n_parts; ++k)
+            RAC_REQUIRE(!parts[k].tex_rgb8 || (h_uv && parts[k].tex_w > 0 && parts[k].tex_h > 0),
+                        "rac_mesh_create_parts: part %d has a texture but no uv / size", k);
+    }
 
     int dev = 0;
     RAC_CUDA_CHECK(cudaGetDevice(&dev));
@@ -148,9 +158,19 @@ int rac_mesh_create(const float* h_verts, int V, const int32_t* h_faces, int T,
         double len = sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
         for (int k = 0; k < 3; ++k) fn[3 * (size_t)t + k] = len > 0.0 ? (float)(n[k] / len) : 0.0f;
     }
+    // mip chains: the mesh's own texture first, then one chain per textured part
     std::vector<uchar4> mips;
     int nmips = 0;
     if (h_tex) build_mips(h_tex, tw, th, mips, nmips);
+    std::vector<size_t> part_mip_off((size_t)(n_parts > 0 ? n_parts : 0), 0);
+    std::vector<int> part_nmips((size_t)(n_parts > 0 ? n_parts : 0), 0);
+    for (int k = 0; k < n_parts; ++k)
+        if (parts[k].tex_rgb8) {
+            part_mip_off[k] = mips.size();
+            std::vector<uchar4> chain;
+            build_mips(parts[k].tex_rgb8, parts[k].tex_w, parts[k].tex_h, chain, part_nmips[k]);
+            mips.insert(mips.end(), chain.begin(), chain.end());
+        }
 
     const size_t o_verts = 0;
     const size_t o_faces = align_up(o_verts + sizeof(float) * 3 * V, 256);
@@ -158,10 +178,28 @@ int rac_mesh_create(const float* h_verts, int V, const int32_t* h_faces, int T,
     const size_t o_uv = align_up(o_fn + sizeof(float) * 3 * T, 256);
     const size_t o_vc = align_up(o_uv + (h_uv ? sizeof(float) * 2 * V : 0), 256);
     const size_t o_tex = align_up(o_vc + (h_vcolor ? sizeof(uchar4) * V : 0), 256);
-    const size_t total = align_up(o_tex + sizeof(uchar4) * mips.size(), 256);
+    const size_t o_parts = align_up(o_tex + sizeof(uchar4) * mips.size(), 256);
+    const size_t o_fpart = align_up(o_parts + sizeof(PartDev) * (size_t)(n_parts > 0 ? n_parts : 0), 256);
+    const size_t total = align_up(o_fpart + (n_parts > 0 ? (size_t)T : 0), 256);
 
     char* blk = nullptr;
     RAC_CUDA_CHECK(cudaMalloc(&blk, total));
+    std::vector<PartDev> pd((size_t)(n_parts > 0 ? n_parts : 0));
+    for (int k = 0; k < n_parts; ++k) {
+        PartDev& q = pd[k];
+        memset(&q, 0, sizeof(q));
+        for (int c = 0; c < 4; ++c) q.base_color[c] = parts[k].material.base_color[c];
+        q.metallic = parts[k].material.metallic;
+        const float rough = fminf(fmaxf(parts[k].material.roughness, 0.04f), 1.0f);     // (same formulas as make_shade_ctx)
+        const float alpha = rough * rough;
+        q.alpha2 = alpha * alpha;
+        q.kgeo = (rough + 1.0f) * (rough + 1.0f) * 0.125f;
+        q.has_vcolor = parts[k].use_vertex_color ? 1 : 0;
+        if (parts[k].tex_rgb8) {
+            q.tex = (const uchar4*)(blk + o_tex) + part_mip_off[k];
+            q.tw = parts[k].tex_w; q.th = parts[k].tex_h; q.nmips = part_nmips[k];
+        }
+    }
     cudaError_t e = cudaMemcpy(blk + o_verts, h_verts, sizeof(float) * 3 * V, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(blk + o_faces, h_faces, sizeof(int) * 3 * T, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(blk + o_fn, fn.data(), sizeof(float) * 3 * T, cudaMemcpyHostToDevice);
@@ -169,6 +207,8 @@ int rac_mesh_create(const float* h_verts, int V, const int32_t* h_faces, int T,
     if (e == cudaSuccess && h_vcolor) e = cudaMemcpy(blk + o_vc, h_vcolor, sizeof(uchar4) * V, cudaMemcpyHostToDevice);
     if (e == cudaSuccess && !mips.empty())
         e = cudaMemcpy(blk + o_tex, mips.data(), sizeof(uchar4) * mips.size(), cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && n_parts > 0) e = cudaMemcpy(blk + o_parts, pd.data(), sizeof(PartDev) * n_parts, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && n_parts > 0) e = cudaMemcpy(blk + o_fpart, h_face_part, (size_t)T, cudaMemcpyHostToDevice);
 
     MeshDev md;
     memset(&md, 0, sizeof(md));
@@ -183,6 +223,8 @@ int rac_mesh_create(const float* h_verts, int V, const int32_t* h_faces, int T,
     md.tw = h_tex ? tw : 0;
     md.th = h_tex ? th : 0;
     md.nmips = nmips;
+    md.parts = n_parts > 0 ? (const PartDev*)(blk + o_parts) : nullptr;
+    md.face_part = n_parts > 0 ? (const unsigned char*)(blk + o_fpart) : nullptr;
     rac_material_t m;
     rac_material_defaults(&m);
     if (mat) m = *mat;
@@ -202,6 +244,19 @@ int rac_mesh_create(const float* h_verts, int V, const int32_t* h_faces, int T,
     g_meshes[slot].d_block = blk;
     *out = slot;
     return RAC_OK;
+}
+
+int rac_mesh_create(const float* h_verts, int V, const int32_t* h_faces, int T,
+                    const float* h_uv, const uint8_t* h_tex, int tw, int th,
+                    const uint8_t* h_vcolor, const rac_material_t* mat, rac_mesh_t* out) {
+    return mesh_create_common(h_verts, V, h_faces, T, h_uv, h_tex, tw, th, h_vcolor, mat, nullptr, 0, nullptr, out);
+}
+
+int rac_mesh_create_parts(const float* h_verts, int V, const int32_t* h_faces, int T,
+                          const float* h_uv, const uint8_t* h_vcolor,
+                          const uint8_t* h_face_part, int n_parts, const rac_part_t* parts, rac_mesh_t* out) {
+    RAC_REQUIRE(n_parts > 0, "rac_mesh_create_parts: n_parts=%d must be positive", n_parts);
+    return mesh_create_common(h_verts, V, h_faces, T, h_uv, nullptr, 0, 0, h_vcolor, nullptr, h_face_part, n_parts, parts, out);
 }
 
 int rac_mesh_destroy(rac_mesh_t mesh) {

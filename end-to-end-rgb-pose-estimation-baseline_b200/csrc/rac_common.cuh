@@ -59,6 +59,16 @@ extern std::atomic<long long> g_launches;
     } while (0)
 
 // ---- device-resident mesh table ---------------------------------------------
+// One primitive ("part") of a multi-material mesh (a .glb scene: renderer.py:36-42 adds every geometry of the file as
+// its own pyrender mesh, each with the material the file gives it).  Shading constants are precomputed on the host.
+struct PartDev {
+    float base_color[4];
+    float metallic, alpha2, kgeo;   // alpha2 = roughness^4, kgeo = (roughness + 1)^2 / 8 (roughness clamped to [0.04, 1])
+    int has_vcolor;                 // COLOR_0 applies to this part (parts without a material, pyrender's default one)
+    const uchar4* tex;              // this part's mip chain, or nullptr
+    int tw, th, nmips, pad;
+};
+
 struct MeshDev {
     const float*   verts;     // V*3 object-frame positions
     const int*     faces;     // T*3 vertex indices
@@ -70,6 +80,8 @@ struct MeshDev {
     int tw, th, nmips;
     float base_color[4];
     float metallic, roughness;
+    const PartDev* parts;         // multi-part meshes only (else nullptr): per-part material / texture ...
+    const unsigned char* face_part;   // ... selected per face, T entries
 };
 
 constexpr int kMaxMeshes = 4096;

@@ -25,6 +25,8 @@ struct ShadeCtx {
     const float* uv;
     const uchar4* tex;
     int tw, th, nmips;
+    const PartDev* parts;               // multi-part meshes (GLB scenes): material / texture per face
+    const unsigned char* face_part;
 };
 
 __device__ __forceinline__ float clamp01(float x) { return fminf(fmaxf(x, 0.0f), 1.0f); }
@@ -75,13 +77,22 @@ __device__ __noinline__ void shade_base_color(const ShadeCtx& sc, const int4* __
         persp_bary(g, Pcx, Pcy, w0, w1, w2);
         // record order is (v0, v2, v1) of the mesh face (setup swaps v1 <-> v2)
         const int i0 = sc.faces[3 * tri], i1 = sc.faces[3 * tri + 2], i2 = sc.faces[3 * tri + 1];
-        if (sc.vcolor) {
+        // multi-part meshes: the face's own texture; COLOR_0 only where the part asks for it
+        const uchar4* tex = sc.tex;
+        int tw = sc.tw, th = sc.th, nmips = sc.nmips;
+        bool use_vc = sc.vcolor != nullptr;
+        if (sc.parts) {
+            const PartDev& pt = sc.parts[sc.face_part[tri]];
+            tex = pt.tex; tw = pt.tw; th = pt.th; nmips = pt.nmips;
+            use_vc = use_vc && pt.has_vcolor;
+        }
+        if (use_vc) {
             const uchar4 c0 = sc.vcolor[i0], c1 = sc.vcolor[i1], c2 = sc.vcolor[i2];
             base[0] *= clamp01((w0 * c0.x + w1 * c1.x + w2 * c2.x) * (1.0f / 255.0f));
             base[1] *= clamp01((w0 * c0.y + w1 * c1.y + w2 * c2.y) * (1.0f / 255.0f));
             base[2] *= clamp01((w0 * c0.z + w1 * c1.z + w2 * c2.z) * (1.0f / 255.0f));
         }
-        if (sc.tex) {
+        if (tex) {
             const float u = w0 * sc.uv[2 * i0] + w1 * sc.uv[2 * i1] + w2 * sc.uv[2 * i2];
             const float v = w0 * sc.uv[2 * i0 + 1] + w1 * sc.uv[2 * i1 + 1] + w2 * sc.uv[2 * i2 + 1];
             // LOD from one-pixel finite differences on the triangle's plane (GL quad derivatives)
@@ -92,16 +103,16 @@ __device__ __noinline__ void shade_base_color(const ShadeCtx& sc, const int4* __
             const float vx = wx0 * sc.uv[2 * i0 + 1] + wx1 * sc.uv[2 * i1 + 1] + wx2 * sc.uv[2 * i2 + 1] - v;
             const float uy = wy0 * sc.uv[2 * i0] + wy1 * sc.uv[2 * i1] + wy2 * sc.uv[2 * i2] - u;
             const float vy = wy0 * sc.uv[2 * i0 + 1] + wy1 * sc.uv[2 * i1 + 1] + wy2 * sc.uv[2 * i2 + 1] - v;
-            const float rx2 = ux * ux * sc.tw * sc.tw + vx * vx * sc.th * sc.th;
-            const float ry2 = uy * uy * sc.tw * sc.tw + vy * vy * sc.th * sc.th;
+            const float rx2 = ux * ux * tw * tw + vx * vx * th * th;
+            const float ry2 = uy * uy * tw * tw + vy * vy * th * th;
             float lod = 0.5f * log2f(fmaxf(fmaxf(rx2, ry2), 1e-20f));
-            lod = fminf(fmaxf(lod, 0.0f), (float)(sc.nmips - 1));
+            lod = fminf(fmaxf(lod, 0.0f), (float)(nmips - 1));
             const int l0 = (int)floorf(lod);
-            const int l1 = min(l0 + 1, sc.nmips - 1);
+            const int l1 = min(l0 + 1, nmips - 1);
             const float fl = lod - (float)l0;
             // walk the mip chain to level l0
-            const uchar4* lvl = sc.tex;
-            int w = sc.tw, h = sc.th;
+            const uchar4* lvl = tex;
+            int w = tw, h = th;
             for (int l = 0; l < l0; ++l) { lvl += (size_t)w * h; w = max(w >> 1, 1); h = max(h >> 1, 1); }
             float3 ta = tex_bilinear(lvl, w, h, u, v);
             if (l1 != l0) {
@@ -126,7 +137,10 @@ struct ShadeTri {
 
 // RS-S: shade triangle `tri` at the centre of pixel (px,py); returns RGBA8 packed little-endian.
 // `rec` (the record in global memory) is only read for vertex-coloured / textured meshes.
-__device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const ShadeTri& t, const int4* __restrict__ rec, unsigned tri, int px, int py) {
+// PARTS: the mesh is multi-part (GLB scene) — material and texture come from the face's part.  Compiled as a separate,
+// out-of-line copy (shade_parts) so that the single-material hot path keeps its register allocation.
+template <bool PARTS>
+__device__ __forceinline__ unsigned shade_t(const ShadeCtx& sc, const ShadeTri& t, const int4* __restrict__ rec, unsigned tri, int px, int py) {
     const float nx = t.nx, ny = t.ny, nz = t.nz;
     const int Pcx = px * kSubpix + 128, Pcy = py * kSubpix + 128;
     float iz = fmaf(t.gy, (float)(Pcy - t.Y0), fmaf(t.gx, (float)(Pcx - t.X0), t.iz0));
@@ -148,13 +162,18 @@ __device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const ShadeTri& t,
     const float radiance = att * sc.intensity;
 
     float base[3] = {sc.base[0], sc.base[1], sc.base[2]};
-    if (sc.vcolor || sc.tex) shade_base_color(sc, rec, tri, Pcx, Pcy, base);   // out of line: cold for untextured meshes
+    float metallic = sc.metallic, alpha2 = sc.alpha2, kk = sc.kgeo;
+    if (PARTS) {
+        const PartDev& pt = sc.parts[sc.face_part[tri]];
+        base[0] = pt.base_color[0]; base[1] = pt.base_color[1]; base[2] = pt.base_color[2];
+        metallic = pt.metallic; alpha2 = pt.alpha2; kk = pt.kgeo;
+    }
+    if (PARTS || sc.vcolor || sc.tex) shade_base_color(sc, rec, tri, Pcx, Pcy, base);   // out of line: cold for untextured meshes
 
     // metallic-roughness BRDF with v = l = h: vh = 1 -> Fresnel = f0
-    const float kk = sc.kgeo;
     const float G = __fdividef(nl, nl * (1.0f - kk) + kk) * __fdividef(nv, nv * (1.0f - kk) + kk);
-    const float dd = nh * nh * (sc.alpha2 - 1.0f) + 1.0f;
-    const float D = __fdividef(sc.alpha2, 3.14159265358979f * dd * dd);
+    const float dd = nh * nh * (alpha2 - 1.0f) + 1.0f;
+    const float D = __fdividef(alpha2, 3.14159265358979f * dd * dd);
     const float spec_common = __fdividef(G * D, 4.0f * nl * nv + 1e-4f);
     unsigned out = 0xFF000000u;
     // untextured default material: r = g = b, one gamma evaluation serves all three channels
@@ -163,8 +182,8 @@ __device__ __forceinline__ unsigned shade(const ShadeCtx& sc, const ShadeTri& t,
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
         if (c > 0 && gray) { out |= qfirst << (8 * c); continue; }
-        const float f0 = 0.04f + (base[c] - 0.04f) * sc.metallic;
-        const float cdiff = base[c] * 0.96f * (1.0f - sc.metallic);
+        const float f0 = 0.04f + (base[c] - 0.04f) * metallic;
+        const float cdiff = base[c] * 0.96f * (1.0f - metallic);
         const float diffuse = (1.0f - f0) * cdiff * (1.0f / 3.14159265358979f);
         const float col = nl * radiance * (diffuse + f0 * spec_common) + base[c] * sc.ambient;
         const float enc = clamp01(__powf(fmaxf(col, 0.0f), 1.0f / 2.2f));
@@ -188,6 +207,7 @@ __device__ __forceinline__ ShadeCtx make_shade_ctx(const MeshDev& mesh, const Ca
     sc.kgeo = (rough + 1.0f) * (rough + 1.0f) * 0.125f;
     sc.vcolor = mesh.vcolor; sc.faces = mesh.faces; sc.uv = mesh.uv; sc.tex = mesh.tex;
     sc.tw = mesh.tw; sc.th = mesh.th; sc.nmips = mesh.nmips;
+    sc.parts = mesh.parts; sc.face_part = mesh.face_part;
     return sc;
 }
 

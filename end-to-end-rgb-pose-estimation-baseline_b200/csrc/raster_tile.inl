@@ -259,6 +259,47 @@ struct TileAcc {
     double dsum, dsumsq;
 };
 
+// R2 of resolve_bin: shade the listed (pixel, representative sample) items, 256 per step.
+template <bool FINAL, bool PARTS>
+__device__ __forceinline__ void shade_items(RasterSmem& sm, const BinCtx& bc, const ShadeCtx* s_sc, int nitems) {
+    const int tid = threadIdx.x;
+    const unsigned short* sitems = sm.items;
+    unsigned* cols = sm.cols;
+    const ShadeCtx& sc = *s_sc;     // built once per bin by the last thread, long before this point; read in place
+                                    // (shared memory): keeps ~28 values out of the registers of the shading loop
+    for (int it = tid; it < nitems; it += kRasterThreads) {
+        const int code = sitems[it];
+        const int p = code & 1023, s = code >> 10;
+        const unsigned key = sm.z[s * kTilePix + p];
+        const unsigned id1 = (key & 0xFFu) - 1u;
+        const unsigned tri = sm.slots[id1];
+        const int4* slot = reinterpret_cast<const int4*>(sm.tri + id1 * kTriStride);
+        const int4 d = slot[3], e = slot[4];
+        ShadeTri st;
+        st.X0 = d.z; st.Y0 = d.w; st.gy = __int_as_float(d.x); st.iz0 = __int_as_float(d.y);
+        st.nx = __int_as_float(e.x); st.ny = __int_as_float(e.y); st.nz = __int_as_float(e.z); st.gx = __int_as_float(e.w);
+        const unsigned col = shade_t<PARTS>(sc, st, bc.img_recs + 3 * (size_t)tri, tri, bc.x_lo + (p & (kTileW - 1)), bc.y_lo + p / kTileW);
+        if (FINAL) {
+            cols[s * kTilePix + p] = col;      // R3 finds it through the representative index
+        } else {
+            // commit: every sample of this pixel won by the same triangle gets the colour; the ids are cleared
+#pragma unroll
+            for (int s2 = 0; s2 < 4; ++s2) {
+                const unsigned k2 = sm.z[s2 * kTilePix + p];
+                if (s2 >= s && k2 != kKeyEmpty32 && ((k2 ^ key) & 0xFFu) == 0u) {
+                    cols[s2 * kTilePix + p] = col;     // stays there: only the final resolve writes cols again, and only
+                                                       // at representative samples of live ids
+                    sm.z[s2 * kTilePix + p] = k2 & ~0xFFu;
+                }
+            }
+        }
+    }
+}
+template <bool FINAL>
+__device__ __noinline__ void shade_items_parts(RasterSmem& sm, const BinCtx& bc, const ShadeCtx* s_sc, int nitems) {
+    shade_items<FINAL, true>(sm, bc, s_sc, nitems);
+}
+
 // Flattened shading.  R1: every pixel finds the distinct uncommitted winners among its 4 samples and lists one
 // (pixel, representative sample) item per distinct triangle; R2: the items are shaded 256 at a time (no lane idles on
 // background or waits for a neighbour's 4-triangle edge pixel); R3 (FINAL): every pixel averages its samples' colours
@@ -319,35 +360,10 @@ __device__ __forceinline__ void resolve_bin(RasterSmem& sm, int* q_count, const 
     RAC_PHASE(7);
     const int nitems = *q_count;
     if (nitems > 0) {       // CTA-uniform
-        const ShadeCtx& sc = *s_sc;     // built once per bin by the last thread, long before this point; read in place
-                                        // (shared memory): keeps ~28 values out of the registers of the shading loop
-        for (int it = tid; it < nitems; it += kRasterThreads) {
-            const int code = sitems[it];
-            const int p = code & 1023, s = code >> 10;
-            const unsigned key = sm.z[s * kTilePix + p];
-            const unsigned id1 = (key & 0xFFu) - 1u;
-            const unsigned tri = sm.slots[id1];
-            const int4* slot = reinterpret_cast<const int4*>(sm.tri + id1 * kTriStride);
-            const int4 d = slot[3], e = slot[4];
-            ShadeTri st;
-            st.X0 = d.z; st.Y0 = d.w; st.gy = __int_as_float(d.x); st.iz0 = __int_as_float(d.y);
-            st.nx = __int_as_float(e.x); st.ny = __int_as_float(e.y); st.nz = __int_as_float(e.z); st.gx = __int_as_float(e.w);
-            const unsigned col = shade(sc, st, bc.img_recs + 3 * (size_t)tri, tri, bc.x_lo + (p & (kTileW - 1)), bc.y_lo + p / kTileW);
-            if (FINAL) {
-                cols[s * kTilePix + p] = col;      // R3 finds it through the representative index
-            } else {
-                // commit: every sample of this pixel won by the same triangle gets the colour; the ids are cleared
-#pragma unroll
-                for (int s2 = 0; s2 < 4; ++s2) {
-                    const unsigned k2 = sm.z[s2 * kTilePix + p];
-                    if (s2 >= s && k2 != kKeyEmpty32 && ((k2 ^ key) & 0xFFu) == 0u) {
-                        cols[s2 * kTilePix + p] = col;     // stays there: only the final resolve writes cols again, and only
-                                                           // at representative samples of live ids
-                        sm.z[s2 * kTilePix + p] = k2 & ~0xFFu;
-                    }
-                }
-            }
-        }
+        // multi-part meshes (GLB scenes: material / texture per face) take an out-of-line copy of the loop, so the
+        // single-material path keeps its register allocation
+        if (s_sc->parts) shade_items_parts<FINAL>(sm, bc, s_sc, nitems);
+        else shade_items<FINAL, false>(sm, bc, s_sc, nitems);
     }
     RAC_PHASE(8);
     __syncthreads();

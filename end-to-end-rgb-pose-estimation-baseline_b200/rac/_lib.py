@@ -21,6 +21,11 @@ class RacMaterial(ctypes.Structure):
     _fields_ = [("base_color", c_float * 4), ("metallic", c_float), ("roughness", c_float)]
 
 
+class RacPart(ctypes.Structure):
+    _fields_ = [("material", RacMaterial), ("tex_rgb8", c_void_p), ("tex_w", c_int), ("tex_h", c_int),
+                ("use_vertex_color", c_int)]
+
+
 class RacScene(ctypes.Structure):
     _fields_ = [("ambient", c_float), ("light_intensity", c_float), ("inner_cone", c_float),
                 ("outer_cone", c_float), ("znear", c_float), ("zfar", c_float)]
@@ -36,6 +41,7 @@ SIGNATURES = {
     "rac_material_defaults": (None, [ctypes.POINTER(RacMaterial)]),
     "rac_mesh_create": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_void_p,
                                 ctypes.POINTER(RacMaterial), c_int_p]),
+    "rac_mesh_create_parts": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int_p]),
     "rac_mesh_destroy": (c_int, [c_int]),
     "rac_mesh_info": (c_int, [c_int, c_int_p, c_int_p]),
     "rac_render_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),

@@ -33,6 +33,9 @@ class Mesh:
         self.tex = None if tex is None else np.ascontiguousarray(tex, dtype=np.uint8)
         # (base_color[4], metallic, roughness); None = pyrender's default material (R7)
         self.material = material
+        # multi-part meshes (GLB scenes, rac/gltf.py): part index per face + [dict(material, tex, use_vcolor)] per part
+        self.face_part = None
+        self.parts = None
         assert self.faces.size == 0 or (self.faces.min() >= 0 and self.faces.max() < len(self.verts))
 
     @property
@@ -181,7 +184,10 @@ def load_mesh(path):
         z = np.load(path)
         get = lambda k: z[k] if k in z.files else None
         return Mesh(z["verts"], z["faces"], uv=get("uv"), vcolor=get("vcolor"), tex=get("tex"), material=get("material"))
-    raise ValueError(f"unsupported mesh format {ext!r} (PLY and NPZ are supported; the reference's datasets are PLY)")
+    if ext == ".glb":   # the reference's "texturized" datasets (renderer.py:36-46)
+        from .gltf import load_glb
+        return load_glb(path)
+    raise ValueError(f"unsupported mesh format {ext!r} (PLY, GLB and NPZ are supported)")
 
 
 # ---- procedural meshes (synthetic inputs: the reference's datasets are unavailable) ----
@@ -309,23 +315,40 @@ class DeviceMesh:
         L = _lib.lib()
         self.mesh = mesh
         self.V, self.T = len(mesh.verts), len(mesh.faces)
-        mat = _lib.RacMaterial()
-        arr = mesh.material_array()
-        for i in range(4):
-            mat.base_color[i] = float(arr[i])
-        mat.metallic, mat.roughness = float(arr[4]), float(arr[5])
-        tw = th = 0
-        tex_p = None
-        if mesh.tex is not None and mesh.uv is not None:
-            th, tw = mesh.tex.shape[:2]
-            tex_p = mesh.tex.ctypes.data_as(ctypes.c_void_p)
         h = ctypes.c_int(-1)
-        rc = L.rac_mesh_create(mesh.verts.ctypes.data_as(ctypes.c_void_p), self.V,
-                               mesh.faces.ctypes.data_as(ctypes.c_void_p), self.T,
-                               mesh.uv.ctypes.data_as(ctypes.c_void_p) if mesh.uv is not None else None,
-                               tex_p, tw, th,
-                               mesh.vcolor.ctypes.data_as(ctypes.c_void_p) if mesh.vcolor is not None else None,
-                               ctypes.byref(mat), ctypes.byref(h))
+        vp = lambda a: a.ctypes.data_as(ctypes.c_void_p) if a is not None else None
+        if getattr(mesh, "parts", None):
+            n = len(mesh.parts)
+            arr = (_lib.RacPart * n)()
+            self._keep = []                     # texture arrays must outlive the call
+            for k, p in enumerate(mesh.parts):
+                m = np.asarray(p["material"], dtype=np.float32).reshape(6)
+                for i in range(4):
+                    arr[k].material.base_color[i] = float(m[i])
+                arr[k].material.metallic, arr[k].material.roughness = float(m[4]), float(m[5])
+                arr[k].use_vertex_color = int(bool(p.get("use_vcolor", False)))
+                tex = p.get("tex")
+                if tex is not None and mesh.uv is not None:
+                    tex = np.ascontiguousarray(tex, dtype=np.uint8)
+                    self._keep.append(tex)
+                    arr[k].tex_rgb8 = tex.ctypes.data_as(ctypes.c_void_p)
+                    arr[k].tex_h, arr[k].tex_w = tex.shape[:2]
+            fp = np.ascontiguousarray(mesh.face_part, dtype=np.uint8)
+            rc = L.rac_mesh_create_parts(vp(mesh.verts), self.V, vp(mesh.faces), self.T, vp(mesh.uv), vp(mesh.vcolor),
+                                         vp(fp), n, arr, ctypes.byref(h))
+        else:
+            mat = _lib.RacMaterial()
+            arr = mesh.material_array()
+            for i in range(4):
+                mat.base_color[i] = float(arr[i])
+            mat.metallic, mat.roughness = float(arr[4]), float(arr[5])
+            tw = th = 0
+            tex_p = None
+            if mesh.tex is not None and mesh.uv is not None:
+                th, tw = mesh.tex.shape[:2]
+                tex_p = mesh.tex.ctypes.data_as(ctypes.c_void_p)
+            rc = L.rac_mesh_create(vp(mesh.verts), self.V, vp(mesh.faces), self.T, vp(mesh.uv), tex_p, tw, th,
+                                   vp(mesh.vcolor), ctypes.byref(mat), ctypes.byref(h))
         _lib.check(rc)
         self.handle = h.value
 
@@ -335,18 +358,45 @@ class DeviceMesh:
             self.handle = -1
 
 
-_cache = {}
+# Path / object -> uploaded mesh, least recently used first.  The reference re-parses the file for every image and keeps
+# nothing; training draws from thousands of distinct ModelNet10 files (roughly 4.7 k across train + validation), more
+# than the library's device table holds (kMaxMeshes = 4096, rac_common.cuh), so the cache is BOUNDED: beyond
+# MAX_DEVICE_MESHES entries the least recently used mesh is destroyed (rac_mesh_destroy synchronises the device first:
+# a batch in flight may still read it) and simply uploaded again if it is ever drawn again.
+import collections
+
+MAX_DEVICE_MESHES = 1024
+MAX_HOST_MESHES = 4096
+_cache = collections.OrderedDict()
 _cache_lock = threading.Lock()
-_host_cache = {}
+_host_cache = collections.OrderedDict()
+
+
+def _cache_get(key, make):
+    """LRU lookup / insert under _cache_lock (the caller holds it)."""
+    dm = _cache.get(key)
+    if dm is not None:
+        _cache.move_to_end(key)
+        return dm
+    while len(_cache) >= MAX_DEVICE_MESHES:
+        _, old = _cache.popitem(last=False)
+        old.destroy()
+    dm = _cache[key] = make()
+    return dm
 
 
 def host_mesh(path):
     """Parsed-once host mesh by path."""
     key = os.path.abspath(path)
     with _cache_lock:
-        if key not in _host_cache:
-            _host_cache[key] = load_mesh(key)
-        return _host_cache[key]
+        hm = _host_cache.get(key)
+        if hm is None:
+            while len(_host_cache) >= MAX_HOST_MESHES:
+                _host_cache.popitem(last=False)
+            hm = _host_cache[key] = load_mesh(key)
+        else:
+            _host_cache.move_to_end(key)
+        return hm
 
 
 def device_mesh(path_or_mesh):
@@ -354,17 +404,12 @@ def device_mesh(path_or_mesh):
     if isinstance(path_or_mesh, DeviceMesh):
         return path_or_mesh
     if isinstance(path_or_mesh, Mesh):
-        key = ("obj", id(path_or_mesh))
         with _cache_lock:
-            if key not in _cache:
-                _cache[key] = DeviceMesh(path_or_mesh)
-            return _cache[key]
+            return _cache_get(("obj", id(path_or_mesh)), lambda: DeviceMesh(path_or_mesh))
     key = os.path.abspath(path_or_mesh)
     hm = host_mesh(key)
     with _cache_lock:
-        if key not in _cache:
-            _cache[key] = DeviceMesh(hm)
-        return _cache[key]
+        return _cache_get(key, lambda: DeviceMesh(hm))
 
 
 def clear_cache():

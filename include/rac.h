@@ -92,6 +92,22 @@ RAC_API int rac_mesh_create(const float* h_verts, int V, const int32_t* h_faces,
                             const float* h_uv, const uint8_t* h_tex, int tw, int th,
                             const uint8_t* h_vcolor, const rac_material_t* mat,
                             rac_mesh_t* out);
+/* Multi-part mesh: what add_object builds from a .glb (renderer.py:36-42: every geometry of the trimesh Scene becomes
+ * its own pyrender mesh, with the file's own glTF material, in ONE scene and one depth buffer).  The primitives are
+ * merged into one indexed mesh; h_face_part (T bytes) names the part of every face, parts[k] its
+ * pbrMetallicRoughness material (baseColorFactor, metallicFactor, roughnessFactor, baseColorTexture as RGB8, row 0 =
+ * v 0) and whether COLOR_0 modulates it (pyrender applies vertex colours only to primitives WITHOUT a material).
+ * h_uv (V,2) / h_vcolor (V,4) cover all vertices (zeros / 255 where a part has none). */
+typedef struct rac_part {
+    rac_material_t material;
+    const uint8_t* tex_rgb8;    /* (tex_h, tex_w, 3) or NULL */
+    int tex_w, tex_h;
+    int use_vertex_color;
+} rac_part_t;
+RAC_API int rac_mesh_create_parts(const float* h_verts, int V, const int32_t* h_faces, int T,
+                                  const float* h_uv, const uint8_t* h_vcolor,
+                                  const uint8_t* h_face_part, int n_parts, const rac_part_t* parts,
+                                  rac_mesh_t* out);
 RAC_API int rac_mesh_destroy(rac_mesh_t mesh);
 RAC_API int rac_mesh_info(rac_mesh_t mesh, int* V, int* T);
 

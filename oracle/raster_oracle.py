@@ -22,6 +22,8 @@ def lib():
         vp, ci = ctypes.c_void_p, ctypes.c_int
         L.oracle_render_batch.restype = ci
         L.oracle_render_batch.argtypes = [vp, ci, vp, ci, vp, vp, vp, ci, ci, vp, vp, vp, vp, ci, ci, ci, vp, vp, vp, ci]
+        L.oracle_render_batch_parts.restype = ci
+        L.oracle_render_batch_parts.argtypes = [vp, ci, vp, ci, vp, vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, vp, vp, vp, ci]
         L.oracle_prepare_model_input.restype = ci
         L.oracle_prepare_model_input.argtypes = [vp, vp, vp, ci, ci, ci, ci, vp, ci]
         L.oracle_num_threads.restype = ci
@@ -53,8 +55,22 @@ def render_batch(mesh, T_CO, K, img_size, scene=None, nthreads=0, want_rgba8=Tru
     rgb = np.empty((B, H, W, 3), dtype=np.float32)
     depth = np.empty((B, H, W), dtype=np.float32)
     rgba8 = np.empty((B, H, W, 4), dtype=np.uint8) if want_rgba8 else None
-    rc = lib().oracle_render_batch(_p(verts), len(verts), _p(faces), len(faces), _p(uv), _p(vc), _p(tex), tw, th,
-                                   _p(mat), _p(sc), _p(T), _p(Kc), B, W, H, _p(rgb), _p(depth), _p(rgba8), int(nthreads))
+    parts = getattr(mesh, "parts", None)
+    if parts:       # multi-part mesh (GLB scene): material / texture per face
+        n = len(parts)
+        pmat = np.ascontiguousarray([np.asarray(p["material"], np.float32).reshape(6) for p in parts], dtype=np.float32)
+        texs = [None if (p.get("tex") is None or uv is None) else np.ascontiguousarray(p["tex"], dtype=np.uint8) for p in parts]
+        ptex = (ctypes.c_void_p * n)(*[t.ctypes.data if t is not None else None for t in texs])
+        ptw = np.ascontiguousarray([t.shape[1] if t is not None else 0 for t in texs], dtype=np.int32)
+        pth = np.ascontiguousarray([t.shape[0] if t is not None else 0 for t in texs], dtype=np.int32)
+        puse = np.ascontiguousarray([int(bool(p.get("use_vcolor", False))) for p in parts], dtype=np.int32)
+        fp = np.ascontiguousarray(mesh.face_part, dtype=np.uint8)
+        rc = lib().oracle_render_batch_parts(_p(verts), len(verts), _p(faces), len(faces), _p(uv), _p(vc), _p(fp), n, _p(pmat),
+                                             ctypes.cast(ptex, ctypes.c_void_p), _p(ptw), _p(pth), _p(puse), _p(sc), _p(T), _p(Kc),
+                                             B, W, H, _p(rgb), _p(depth), _p(rgba8), int(nthreads))
+    else:
+        rc = lib().oracle_render_batch(_p(verts), len(verts), _p(faces), len(faces), _p(uv), _p(vc), _p(tex), tw, th,
+                                       _p(mat), _p(sc), _p(T), _p(Kc), B, W, H, _p(rgb), _p(depth), _p(rgba8), int(nthreads))
     if rc != 0:
         raise MemoryError("oracle_render_batch failed")
     return rgb, depth, rgba8

@@ -52,6 +52,16 @@ typedef struct {
     int tw, th;
     float base_color[4];
     float metallic, roughness;
+    /* multi-part meshes (a .glb scene, renderer.py:36-42: every geometry is its own pyrender mesh with the file's
+     * material, all in one scene): per-face part index; per part a material (6 floats), a texture and whether COLOR_0
+     * applies (pyrender: only primitives without a material) */
+    const uint8_t* face_part;     /* T or NULL */
+    int nparts;
+    const float* part_material;   /* nparts*6 */
+    const int* part_use_vcolor;   /* nparts */
+    const int* part_tw;           /* nparts */
+    const int* part_th;
+    const struct Mips_s* part_mips;
 } OMesh;
 
 typedef struct {
@@ -64,7 +74,7 @@ typedef struct {
 } Proj;
 
 /* mip chain for R8: box filter on the encoded 8-bit values (GL_RGBA8 texture, glGenerateMipmap) */
-typedef struct {
+typedef struct Mips_s {
     int n;
     int w[16], h[16];
     uint8_t* lvl[16];   /* RGB8 */
@@ -224,13 +234,24 @@ static void shade(const OMesh* m, const Mips* mp, const OScene* sc, const float*
     att = att * att / dist2;
     float radiance = att * sc->intensity;
 
-    float base[3] = {m->base_color[0], m->base_color[1], m->base_color[2]};
-    if (m->vcolor || mp->n) {
+    const float* bc = m->base_color;
+    float metallic = m->metallic, roughness = m->roughness;
+    int use_vc = m->vcolor != NULL, tw = m->tw, th = m->th;
+    if (m->face_part) {
+        const int part = m->face_part[t];
+        bc = m->part_material + 6 * part;
+        metallic = bc[4]; roughness = bc[5];
+        mp = &m->part_mips[part];
+        tw = m->part_tw[part]; th = m->part_th[part];
+        use_vc = use_vc && m->part_use_vcolor[part];
+    }
+    float base[3] = {bc[0], bc[1], bc[2]};
+    if (use_vc || mp->n) {
         float w[3];
         pbary(s, Pcx, Pcy, w);
         /* Setup order is (v0, v2, v1) of the mesh face */
         int id[3] = {m->faces[3 * t], m->faces[3 * t + 2], m->faces[3 * t + 1]};
-        if (m->vcolor)
+        if (use_vc)
             for (int k = 0; k < 3; ++k) {
                 float v = 0.0f;
                 for (int j = 0; j < 3; ++j) v += w[j] * (float)m->vcolor[4 * (size_t)id[j] + k];
@@ -246,8 +267,8 @@ static void shade(const OMesh* m, const Mips* mp, const OScene* sc, const float*
                     float q = m->uv[2 * (size_t)id[j] + k];
                     uv[k] += w[j] * q; uvx[k] += wx[j] * q; uvy[k] += wy[j] * q;
                 }
-            float dux = (uvx[0] - uv[0]) * m->tw, dvx = (uvx[1] - uv[1]) * m->th;
-            float duy = (uvy[0] - uv[0]) * m->tw, dvy = (uvy[1] - uv[1]) * m->th;
+            float dux = (uvx[0] - uv[0]) * tw, dvx = (uvx[1] - uv[1]) * th;
+            float duy = (uvy[0] - uv[0]) * tw, dvy = (uvy[1] - uv[1]) * th;
             float rho2 = fmaxf(dux * dux + dvx * dvx, duy * duy + dvy * dvy);
             float lod = 0.5f * log2f(fmaxf(rho2, 1e-20f));
             lod = clampf(lod, 0.0f, (float)(mp->n - 1));
@@ -263,7 +284,7 @@ static void shade(const OMesh* m, const Mips* mp, const OScene* sc, const float*
         }
     }
 
-    float rough = clampf(m->roughness, 0.04f, 1.0f);
+    float rough = clampf(roughness, 0.04f, 1.0f);
     float alpha = rough * rough, alpha2 = alpha * alpha;
     float kk = (rough + 1.0f) * (rough + 1.0f) / 8.0f;
     float G = (nl / (nl * (1.0f - kk) + kk)) * (nv / (nv * (1.0f - kk) + kk));
@@ -271,8 +292,8 @@ static void shade(const OMesh* m, const Mips* mp, const OScene* sc, const float*
     float D = alpha2 / ((float)M_PI * dd * dd);
     float spec = G * D / (4.0f * nl * nv + 1e-4f);
     for (int k = 0; k < 3; ++k) {
-        float f0 = 0.04f + (base[k] - 0.04f) * m->metallic;   /* F = f0 because v.h = 1 */
-        float cdiff = base[k] * 0.96f * (1.0f - m->metallic);
+        float f0 = 0.04f + (base[k] - 0.04f) * metallic;   /* F = f0 because v.h = 1 */
+        float cdiff = base[k] * 0.96f * (1.0f - metallic);
         float col = nl * radiance * ((1.0f - f0) * cdiff / (float)M_PI + f0 * spec) + base[k] * sc->ambient;
         float enc = clamp01(powf(fmaxf(col, 0.0f), 1.0f / 2.2f));
         rgba[k] = (uint8_t)(enc * 255.0f + 0.5f);
@@ -376,18 +397,49 @@ static void scene_from(const float* sp, OScene* sc) {
  * material: base_color[4], metallic, roughness.  scene: ambient,intensity,inner,outer,znear,zfar.
  * nthreads <= 0: all available.
  */
+static int render_batch_common(OMesh m, const float* scene, const float* T_CO, const float* K, int B, int W, int H,
+                               float* rgb, float* depth, uint8_t* rgba8, int nthreads);
+
 EXPORT int oracle_render_batch(const float* verts, int V, const int32_t* faces, int Tn, const float* uv,
                                const uint8_t* vcolor, const uint8_t* tex, int tw, int th, const float* material,
                                const float* scene, const float* T_CO, const float* K, int B, int W, int H,
                                float* rgb, float* depth, uint8_t* rgba8, int nthreads) {
     OMesh m;
+    memset(&m, 0, sizeof(m));
     m.verts = verts; m.faces = faces; m.V = V; m.T = Tn; m.uv = uv; m.vcolor = vcolor; m.tex = tex; m.tw = tw; m.th = th;
     for (int k = 0; k < 4; ++k) m.base_color[k] = material[k];
     m.metallic = material[4]; m.roughness = material[5];
+    return render_batch_common(m, scene, T_CO, K, B, W, H, rgb, depth, rgba8, nthreads);
+}
+
+/* Multi-part variant: face_part (T), part_material (nparts*6), part_tex[k] = RGB8 (part_th[k], part_tw[k], 3) or NULL,
+ * part_use_vcolor (nparts). */
+EXPORT int oracle_render_batch_parts(const float* verts, int V, const int32_t* faces, int Tn, const float* uv,
+                                     const uint8_t* vcolor, const uint8_t* face_part, int nparts, const float* part_material,
+                                     const uint8_t* const* part_tex, const int* part_tw, const int* part_th,
+                                     const int* part_use_vcolor, const float* scene, const float* T_CO, const float* K,
+                                     int B, int W, int H, float* rgb, float* depth, uint8_t* rgba8, int nthreads) {
+    OMesh m;
+    memset(&m, 0, sizeof(m));
+    m.verts = verts; m.faces = faces; m.V = V; m.T = Tn; m.uv = uv; m.vcolor = vcolor;
+    m.face_part = face_part; m.nparts = nparts; m.part_material = part_material; m.part_use_vcolor = part_use_vcolor;
+    m.part_tw = part_tw; m.part_th = part_th;
+    Mips* pm = (Mips*)calloc((size_t)nparts, sizeof(Mips));
+    if (!pm) return -1;
+    for (int k = 0; k < nparts; ++k) mips_build(&pm[k], (part_tex[k] && uv) ? part_tex[k] : NULL, part_tw[k], part_th[k]);
+    m.part_mips = pm;
+    int rc = render_batch_common(m, scene, T_CO, K, B, W, H, rgb, depth, rgba8, nthreads);
+    for (int k = 0; k < nparts; ++k) mips_free(&pm[k]);
+    free(pm);
+    return rc;
+}
+
+static int render_batch_common(OMesh m, const float* scene, const float* T_CO, const float* K, int B, int W, int H,
+                               float* rgb, float* depth, uint8_t* rgba8, int nthreads) {
     OScene sc;
     scene_from(scene, &sc);
     Mips mp;
-    mips_build(&mp, (tex && uv) ? tex : NULL, tw, th);
+    mips_build(&mp, (m.tex && m.uv) ? m.tex : NULL, m.tw, m.th);
 #ifdef _OPENMP
     if (nthreads > 0) omp_set_num_threads(nthreads);
 #endif

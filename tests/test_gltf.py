@@ -1,0 +1,106 @@
+"""Binary glTF ingestion (rac/gltf.py) — the loader half of renderer.py:28-48 for the reference's "texturized" meshes:
+every triangle primitive of the file, in its local frame (node transforms ignored, as `scene.geometry.values()` does),
+rotated by Rx(90 deg), with the file's pbrMetallicRoughness material.  CPU only (no device calls)."""
+import json
+import struct
+
+import numpy as np
+import pytest
+
+from rac import gltf
+from rac import mesh as M
+
+
+def _prims():
+    a = M.with_texture(M.icosphere(2), size=32, seed=2)
+    b = M.box(0.5, 0.3, 0.2, 1)
+    vc = np.tile(np.array([[10, 200, 30, 255]], np.uint8), (len(b.verts), 1))
+    return [dict(verts=a.verts, faces=a.faces, uv=a.uv, tex=a.tex, material=(1, 1, 1, 1, 0.1, 0.7)),
+            dict(verts=b.verts + np.float32([0.6, 0, 0]), faces=b.faces, material=(0.8, 0.2, 0.1, 1, 0.5, 0.4), vcolor=vc),
+            dict(verts=b.verts + np.float32([-0.6, 0, 0]), faces=b.faces, vcolor=vc)]
+
+
+def test_roundtrip_matches_the_reference_semantics(tmp_path):
+    prims = _prims()
+    path = str(tmp_path / "scene.glb")
+    gltf.save_glb(path, prims, node_translation=(5, 5, 5))          # a faithful loader ignores the node transform
+    m = M.load_mesh(path)
+    assert len(m.parts) == 3 and m.face_part.dtype == np.uint8
+    nv = np.cumsum([0] + [len(p["verts"]) for p in prims])
+    nf = np.cumsum([0] + [len(p["faces"]) for p in prims])
+    for k, p in enumerate(prims):
+        v = np.asarray(p["verts"], np.float64)
+        want = np.stack([v[:, 0], -v[:, 2], v[:, 1]], 1)             # Rx(90 deg), renderer.py:38-40
+        np.testing.assert_allclose(m.verts[nv[k]:nv[k + 1]], want, atol=1e-7)
+        np.testing.assert_array_equal(m.faces[nf[k]:nf[k + 1]], np.asarray(p["faces"]) + nv[k])
+        assert (m.face_part[nf[k]:nf[k + 1]] == k).all()
+    # materials: the file's own pbrMetallicRoughness, baseColorFactor in 1/255 steps (trimesh keeps it as uint8)
+    np.testing.assert_allclose(m.parts[0]["material"], (1, 1, 1, 1, 0.1, 0.7), atol=1e-7)
+    np.testing.assert_allclose(m.parts[1]["material"], (204 / 255, 51 / 255, 26 / 255, 1, 0.5, 0.4), atol=1e-7)
+    np.testing.assert_array_equal(m.parts[0]["tex"], prims[0]["tex"])
+    np.testing.assert_allclose(m.uv[nv[0]:nv[1]], prims[0]["uv"], atol=1e-7)
+    # COLOR_0: ignored on a primitive WITH a material, used (with pyrender's default material) on one WITHOUT
+    assert not m.parts[1]["use_vcolor"] and (m.vcolor[nv[1]:nv[2]] == 255).all()
+    assert m.parts[2]["use_vcolor"] and (m.vcolor[nv[2]:nv[3]] == [10, 200, 30, 255]).all()
+    np.testing.assert_allclose(m.parts[2]["material"], (0.3, 0.3, 0.3, 1.0, 0.2, 0.8))
+    assert m.parts[1]["tex"] is None and m.parts[2]["tex"] is None
+    # the trimesh-compatible vertex source of data_loaders.get_vertices
+    assert m.vertices is m.verts
+
+
+def test_gltf_defaults_strides_and_errors(tmp_path):
+    """Hand-built file: interleaved (strided) POSITION + TEXCOORD_0 view, uint16 indices, a material that omits every
+    factor (glTF defaults: white, metallic 1, roughness 1), a non-triangle primitive that must be skipped."""
+    pos = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1]], "<f4")
+    uv = np.array([[0, 0], [1, 0], [0, 1], [1, 1]], "<f4")
+    inter = np.concatenate([pos, uv], 1).astype("<f4").tobytes()      # stride 20
+    idx = np.array([0, 1, 2, 0, 2, 3], "<u2").tobytes()
+    blob = inter + idx
+    g = {"asset": {"version": "2.0"}, "buffers": [{"byteLength": len(blob)}],
+         "bufferViews": [{"buffer": 0, "byteOffset": 0, "byteLength": len(inter), "byteStride": 20},
+                         {"buffer": 0, "byteOffset": len(inter), "byteLength": len(idx)}],
+         "accessors": [{"bufferView": 0, "byteOffset": 0, "componentType": 5126, "count": 4, "type": "VEC3"},
+                       {"bufferView": 0, "byteOffset": 12, "componentType": 5126, "count": 4, "type": "VEC2"},
+                       {"bufferView": 1, "componentType": 5123, "count": 6, "type": "SCALAR"}],
+         "materials": [{}],
+         "meshes": [{"primitives": [{"attributes": {"POSITION": 0, "TEXCOORD_0": 1}, "indices": 2, "material": 0},
+                                    {"attributes": {"POSITION": 0}, "indices": 2, "mode": 1}]}]}
+    js = json.dumps(g).encode()
+    js += b" " * (-len(js) % 4)
+    blob += b"\0" * (-len(blob) % 4)
+    path = str(tmp_path / "hand.glb")
+    with open(path, "wb") as f:
+        f.write(struct.pack("<4sII", b"glTF", 2, 12 + 8 + len(js) + 8 + len(blob)))
+        f.write(struct.pack("<I4s", len(js), b"JSON") + js + struct.pack("<I4s", len(blob), b"BIN\0") + blob)
+    m = gltf.load_glb(path)
+    assert len(m.parts) == 1 and len(m.faces) == 2
+    np.testing.assert_allclose(m.parts[0]["material"], (1, 1, 1, 1, 1, 1))
+    np.testing.assert_allclose(m.verts, [[0, 0, 0], [1, 0, 0], [0, 0, 1], [0, -1, 0]], atol=1e-7)
+    np.testing.assert_allclose(m.uv, uv)
+    raw = gltf.load_glb(path, apply_rx90=False)
+    np.testing.assert_allclose(raw.verts, pos)
+    bad = str(tmp_path / "bad.glb")
+    with open(bad, "wb") as f:
+        f.write(b"glTX" + b"\0" * 20)
+    with pytest.raises(ValueError):
+        gltf.load_glb(bad)
+    with pytest.raises(ValueError):
+        M.load_mesh(str(tmp_path / "x.obj"))
+
+
+def test_oracle_renders_every_part_with_its_own_material(tmp_path):
+    """The CPU oracle with per-face parts: each primitive shows its own colour (textured / red factor / green COLOR_0)."""
+    from conftest import intrinsics
+    from oracle import raster_oracle as ro
+    path = str(tmp_path / "scene.glb")
+    gltf.save_glb(path, _prims())
+    m = M.load_mesh(path)
+    T = np.eye(4, dtype=np.float32)[None].copy()
+    T[0, :3, 3] = [0.0, 0.0, 2.5]
+    K = intrinsics(1, 200, 200)
+    _, depth, q = ro.render_batch(m, T, K, 200)
+    assert (depth > 0).mean() > 0.05
+    cov = q[0][depth[0] > 0][:, :3].astype(int)
+    red = (cov[:, 0] > cov[:, 1] + 50) & (cov[:, 0] > cov[:, 2] + 50)
+    green = (cov[:, 1] > cov[:, 0] + 50) & (cov[:, 1] > cov[:, 2] + 50)
+    assert red.sum() > 100 and green.sum() > 100 and (~red & ~green).sum() > 100
