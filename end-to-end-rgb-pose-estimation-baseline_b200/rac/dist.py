@@ -61,11 +61,19 @@ def global_loss_mean(per_sample, global_batch=None):
     return (local_sum - local_sum.detach()) / n + (buf[0] / n).to(per_sample.dtype)
 
 
+def _collective_device():
+    if dist.is_available() and dist.is_initialized() and dist.get_backend() == "nccl":
+        return torch.device("cuda", torch.cuda.current_device())
+    return torch.device("cpu")
+
+
 def first_sample_intrinsics(Ks_local):
     """(fx, fy) of the global batch's first sample (Q2), broadcast from rank 0; Ks_local (b,3,3) may be empty
     on other ranks."""
     rank, ws = world()
-    dev = Ks_local.device if isinstance(Ks_local, torch.Tensor) and dist.is_initialized() and dist.get_backend() == "nccl" else "cpu"
+    # NCCL has no CPU backend: the 2-value buffer is staged on this rank's GPU wherever Ks lives (the reference's
+    # cam_mats stay on the CPU, Q5); gloo (CPU tests) keeps it on the host
+    dev = _collective_device()
     v = torch.zeros(2, dtype=torch.float64, device=dev)
     if rank == 0:
         K0 = torch.as_tensor(Ks_local)[0]

@@ -162,3 +162,22 @@ def test_gt_u8_full_size_through_the_shadow_module(rac):
     assert gt.mean(dim=(1, 2, 3)).abs().max() < 1e-6 and (gt.std(dim=(1, 2, 3), unbiased=False) - 1).abs().max() < 1e-6
     assert torch.equal(x1[:, :3], x3[:, :3])
     torch.testing.assert_close(x1[:, 3:], x3[:, 3:], rtol=1e-5, atol=2e-6)
+
+
+def test_first_sample_intrinsics_under_nccl_with_cpu_cam_mats(monkeypatch):
+    """The reference's cam_mats live on the CPU (Q5) and INTEGRATION.md tells users to pass exactly that; NCCL has no CPU
+    backend, so the broadcast buffer must be staged on this rank's GPU.  One-rank NCCL group, broadcast path forced."""
+    import torch.distributed as dist
+    from rac import dist as rd
+    if dist.is_initialized():
+        pytest.skip("a process group already exists in this process")
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:29541", rank=0, world_size=1,
+                            device_id=torch.device("cuda", torch.cuda.current_device()))
+    try:
+        assert rd._collective_device().type == "cuda"
+        monkeypatch.setattr(rd, "world", lambda: (0, 2))           # take the ws > 1 branch: a real NCCL broadcast
+        Ks = torch.tensor([[[444.0, 0, 160], [0, 333.0, 120], [0, 0, 1]]], dtype=torch.float64).repeat(3, 1, 1)      # CPU, f64
+        assert rd.first_sample_intrinsics(Ks) == (444.0, 333.0)
+        assert rd.first_sample_intrinsics(Ks.cuda()) == (444.0, 333.0)
+    finally:
+        dist.destroy_process_group()

@@ -509,3 +509,26 @@ def test_committed_golden_vectors(rac):
                           for i in range(len(T))])
         compare(out, (rgb_o, depth_o, rgba_o), G.W, G.H, "golden:" + name)
         assert qmax > 0
+
+
+# ---- second source for the (?) items of R5 / R7 / R8: the same closed-form known answers the oracle is held to ----------
+def _gpu_render(rac):
+    def render(mesh, T, K, wh):
+        out = rac.render_batch_device(T, mesh, K, wh, want_rgba8=True)
+        return out["depth"].cpu().numpy(), out["rgba8"].cpu().numpy()
+    return render
+
+
+def test_brdf_closed_form_points(rac):
+    import known_answers as KA
+    KA.check_brdf_points(_gpu_render(rac), tol=2)          # fast-math shading: the colour bar is 2/255
+
+
+def test_resolve_is_the_mean_of_four_samples_and_depth_is_sample_zero(rac):
+    import known_answers as KA
+    KA.check_half_covered_pixels(_gpu_render(rac))
+
+
+def test_texture_lod_of_a_minified_checker(rac):
+    import known_answers as KA
+    KA.check_minified_checker(_gpu_render(rac), tol=2)
