@@ -601,7 +601,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~15 s CPU oracle leg (profiling runs)")
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4", "sweep"],
+                    help="BASELINE.json configs[0..4]; c2 (default) is the metric's shape and the contract line; the others "
+                         "print profiles/configs_bench.py's rows (one JSON object per line)")
     args = ap.parse_args()
+    if args.config != "c2" and args.impl == "ours":
+        sys.argv = [os.path.join(ROOT, "profiles", "configs_bench.py"), "--configs", args.config]
+        import runpy
+        runpy.run_path(sys.argv[0], run_name="__main__")
+        return
     # stdout carries exactly one JSON line: everything else that native libraries print there (NCCL's version banner
     # under torchrun) is sent to stderr by pointing fd 1 at fd 2 and keeping the real stdout for the result line
     global _RESULT_FD
