@@ -54,8 +54,12 @@ __device__ __forceinline__ float3 tex_bilinear(const uchar4* __restrict__ lvl, i
     return r;
 }
 
-// perspective-correct barycentric weights of (v0,v1,v2) (record order) at subpixel point (Px,Py)
-__device__ __forceinline__ void persp_bary(const TriGeom& g, int Px, int Py, float& w0, float& w1, float& w2) {
+// perspective-correct barycentric weights of (v0,v1,v2) (record order) at subpixel point (Px,Py), and — GRAD — at the
+// points one pixel to the right and one pixel down (GL's quad derivatives for the texture LOD).  The screen-space
+// barycentrics are affine, so the neighbours follow from the edge functions' coefficients: one set of exact int64 edge
+// evaluations serves all three points.
+template <bool GRAD>
+__device__ __forceinline__ void persp_bary(const TriGeom& g, int Px, int Py, float (&w)[3], float (&wx)[3], float (&wy)[3]) {
     const long long e0 = (long long)(g.X1 - g.X0) * (Py - g.Y0) - (long long)(g.Y1 - g.Y0) * (Px - g.X0);  // -> v2
     const long long e1 = (long long)(g.X2 - g.X1) * (Py - g.Y1) - (long long)(g.Y2 - g.Y1) * (Px - g.X1);  // -> v0
     const long long e2 = (long long)(g.X0 - g.X2) * (Py - g.Y2) - (long long)(g.Y0 - g.Y2) * (Px - g.X2);  // -> v1
@@ -63,18 +67,39 @@ __device__ __forceinline__ void persp_bary(const TriGeom& g, int Px, int Py, flo
     const float l0 = (float)e1 * inv_area, l1 = (float)e2 * inv_area, l2 = (float)e0 * inv_area;
     const float iz1 = fmaf(g.gy, (float)(g.Y1 - g.Y0), fmaf(g.gx, (float)(g.X1 - g.X0), g.iz0));
     const float iz2 = fmaf(g.gy, (float)(g.Y2 - g.Y0), fmaf(g.gx, (float)(g.X2 - g.X0), g.iz0));
-    float a0 = l0 * g.iz0, a1 = l1 * iz1, a2 = l2 * iz2;
-    const float s = a0 + a1 + a2;
-    const float inv = (fabsf(s) > 1e-30f) ? 1.0f / s : 0.0f;
-    w0 = a0 * inv; w1 = a1 * inv; w2 = a2 * inv;
+    {
+        const float a0 = l0 * g.iz0, a1 = l1 * iz1, a2 = l2 * iz2;
+        const float s = a0 + a1 + a2;
+        const float inv = (fabsf(s) > 1e-30f) ? 1.0f / s : 0.0f;
+        w[0] = a0 * inv; w[1] = a1 * inv; w[2] = a2 * inv;
+    }
+    if (GRAD) {
+        const float k = (float)kSubpix * inv_area;
+        // d(e1)/dPx = -(Y2 - Y1), d(e1)/dPy = X2 - X1 (and cyclically): one pixel = kSubpix subpixels
+        const float l0x = l0 - (float)(g.Y2 - g.Y1) * k, l1x = l1 - (float)(g.Y0 - g.Y2) * k, l2x = l2 - (float)(g.Y1 - g.Y0) * k;
+        const float l0y = l0 + (float)(g.X2 - g.X1) * k, l1y = l1 + (float)(g.X0 - g.X2) * k, l2y = l2 + (float)(g.X1 - g.X0) * k;
+        {
+            const float a0 = l0x * g.iz0, a1 = l1x * iz1, a2 = l2x * iz2;
+            const float s = a0 + a1 + a2;
+            const float inv = (fabsf(s) > 1e-30f) ? 1.0f / s : 0.0f;
+            wx[0] = a0 * inv; wx[1] = a1 * inv; wx[2] = a2 * inv;
+        }
+        {
+            const float a0 = l0y * g.iz0, a1 = l1y * iz1, a2 = l2y * iz2;
+            const float s = a0 + a1 + a2;
+            const float inv = (fabsf(s) > 1e-30f) ? 1.0f / s : 0.0f;
+            wy[0] = a0 * inv; wy[1] = a1 * inv; wy[2] = a2 * inv;
+        }
+    }
 }
 
 // COLOR_0 / texture modulation of the base colour (R7 "x COLOR_0", R8) at subpixel point (Pcx, Pcy).  Kept out of line:
 // the raster warps of an SM run at unrelated program counters, so the kernel's hot instruction footprint matters.
 __device__ __noinline__ void shade_base_color(const ShadeCtx& sc, const int4* __restrict__ rec, unsigned tri, int Pcx, int Pcy, float* base) {
         const TriGeom g = unpack_geom(rec[0], rec[1], rec[2]);
-        float w0, w1, w2;
-        persp_bary(g, Pcx, Pcy, w0, w1, w2);
+        float w[3], wxv[3], wyv[3];
+        persp_bary<true>(g, Pcx, Pcy, w, wxv, wyv);
+        const float w0 = w[0], w1 = w[1], w2 = w[2];
         // record order is (v0, v2, v1) of the mesh face (setup swaps v1 <-> v2)
         const int i0 = sc.faces[3 * tri], i1 = sc.faces[3 * tri + 2], i2 = sc.faces[3 * tri + 1];
         // multi-part meshes: the face's own texture; COLOR_0 only where the part asks for it
@@ -96,9 +121,7 @@ __device__ __noinline__ void shade_base_color(const ShadeCtx& sc, const int4* __
             const float u = w0 * sc.uv[2 * i0] + w1 * sc.uv[2 * i1] + w2 * sc.uv[2 * i2];
             const float v = w0 * sc.uv[2 * i0 + 1] + w1 * sc.uv[2 * i1 + 1] + w2 * sc.uv[2 * i2 + 1];
             // LOD from one-pixel finite differences on the triangle's plane (GL quad derivatives)
-            float wx0, wx1, wx2, wy0, wy1, wy2;
-            persp_bary(g, Pcx + kSubpix, Pcy, wx0, wx1, wx2);
-            persp_bary(g, Pcx, Pcy + kSubpix, wy0, wy1, wy2);
+            const float wx0 = wxv[0], wx1 = wxv[1], wx2 = wxv[2], wy0 = wyv[0], wy1 = wyv[1], wy2 = wyv[2];
             const float ux = wx0 * sc.uv[2 * i0] + wx1 * sc.uv[2 * i1] + wx2 * sc.uv[2 * i2] - u;
             const float vx = wx0 * sc.uv[2 * i0 + 1] + wx1 * sc.uv[2 * i1 + 1] + wx2 * sc.uv[2 * i2 + 1] - v;
             const float uy = wy0 * sc.uv[2 * i0] + wy1 * sc.uv[2 * i1] + wy2 * sc.uv[2 * i2] - u;

@@ -64,6 +64,8 @@ def glb_scene(tmpdir, k, tris):
     body = M.with_texture(M.bumpy_sphere(level=level_for(tris), seed=20 + k, decimate_to=tris - 200), size=256, seed=k)
     b1, b2 = M.box(0.5, 0.12, 0.12, 2), M.box(0.12, 0.5, 0.12, 2)
     path = os.path.join(tmpdir, "texturized_%02d.glb" % k)
+    if os.environ.get("RAC_C3_NOTEX"):          # diagnostic: the same geometry without the texture (cost of R8)
+        body.tex = None
     gltf.save_glb(path, [dict(verts=body.verts, faces=body.faces, uv=body.uv, tex=body.tex, material=(1, 1, 1, 1, 0.0, 0.6)),
                          dict(verts=b1.verts + np.float32([0, 0, 0.42]), faces=b1.faces, material=(0.7, 0.3, 0.2, 1, 0.3, 0.5)),
                          dict(verts=b2.verts + np.float32([0, 0, -0.42]), faces=b2.faces, material=(0.2, 0.4, 0.7, 1, 0.8, 0.4))])
