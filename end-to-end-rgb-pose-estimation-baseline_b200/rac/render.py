@@ -297,6 +297,18 @@ def _host_staging(shape, dtype):
     return ring, i
 
 
+def _pack_threads():
+    """Threads for the host pack: the cores this process may use, shared between the ranks of the node (torchrun
+    exports LOCAL_WORLD_SIZE), at most 16 — the pass is memory-bound."""
+    import os
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        cores = os.cpu_count() or 1
+    ranks = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    return max(1, min(16, cores // ranks))
+
+
 def _pack_host_gt_u8(a):
     """float64 host crop (B,H,W,3) -> (pinned u8 tensor, ring, slot) if every value is an exact PNG code / 255.0
     (image_dataloaders.py:79-83), else None.  One threaded pass over the array (csrc/host_pack.cu)."""
@@ -305,7 +317,7 @@ def _pack_host_gt_u8(a):
     buf = ring["bufs"][slot]
     ok = ctypes.c_int(0)
     rc = L.rac_host_pack_gt_u8(ctypes.c_void_p(a.__array_interface__["data"][0]), 1 if a.dtype == np.float64 else 0,
-                               a.size, ctypes.c_void_p(buf.data_ptr()), 0, ctypes.byref(ok))
+                               a.size, ctypes.c_void_p(buf.data_ptr()), _pack_threads(), ctypes.byref(ok))
     _lib.check(rc)
     return (buf, ring, slot) if ok.value else None
 
