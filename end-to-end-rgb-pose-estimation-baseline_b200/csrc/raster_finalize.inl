@@ -347,6 +347,160 @@ gt_norm_kernel(const float* __restrict__ gt_hwc, float* __restrict__ x_nchw, int
     RAC_TL(0);
 }
 
+// ---------------------------------------------------------------------------------------------
+// gt crop, bulk-copy variant (standalone launches: rac_assemble_input, the end-to-end path of prepare_model_input)
+// ---------------------------------------------------------------------------------------------
+// Same arithmetic, same cluster-per-image decomposition and the same per-thread summation order as gt_norm_kernel (the
+// two are bit-identical), but the bytes move the Blackwell way: every CTA streams its slice of the crop through a
+// two-stage shared-memory ring filled by cp.async.bulk (global -> shared, completion on an mbarrier, no registers in
+// flight), de-interleaves HWC -> three planes in shared memory, and writes each plane chunk back with cp.async.bulk
+// (shared -> global, bulk_group).  One thread issues all copies; the 256 threads only touch shared memory.
+// 48 KB of dynamic shared memory per CTA (2 x 12 KB in, 2 x 12 KB out): 4 CTAs per SM, 96 KB of loads in flight per SM.
+// Not used next to raster_kernel: four raster CTAs leave ~2 KB of shared memory per SM, which is why the co-resident
+// launch of the render path keeps the register-staged kernel above.
+constexpr int kGtChunkQuads = 256;                       // one quad (4 px, 48 B in, 3 x 16 B out) per thread per chunk
+constexpr int kGtStages = 2;
+constexpr int kGtInBytes = kGtChunkQuads * 48;           // 12 KB
+constexpr int kGtPlaneBytes = kGtChunkQuads * 16;        //  4 KB per plane chunk
+constexpr size_t kGtTmaSmem = (size_t)kGtStages * kGtInBytes + 2 * 3 * kGtPlaneBytes;
+
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" :: "r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+// global -> shared bulk copy of `bytes` (multiple of 16), completion counted on `bar`
+__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_u32(bar)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(smem_u32(dst_smem)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* dst, const void* src_smem, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(dst), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+
+__global__ void __launch_bounds__(kGtThreads, 4)
+gt_norm_tma_kernel(const float* __restrict__ gt_hwc, float* __restrict__ x_nchw, int npix, int C, int ch0, int B) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    extern __shared__ __align__(128) unsigned char gt_smem[];
+    float4* s_in = reinterpret_cast<float4*>(gt_smem);                                        // [kGtStages][kGtChunkQuads * 3]
+    float4* s_out = reinterpret_cast<float4*>(gt_smem + (size_t)kGtStages * kGtInBytes);      // [2][3][kGtChunkQuads]
+    __shared__ __align__(8) unsigned long long s_full[kGtStages];
+    __shared__ double s_warp[2][kGtThreads / 32];
+    __shared__ double s_part[2];
+    __shared__ float s_aff[2];
+    const int rank = (int)cluster.block_rank();
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) {
+        for (int s = 0; s < kGtStages; ++s) mbar_init(&s_full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    unsigned it = 0;                      // chunks consumed so far by this CTA: stage = it % kGtStages, parity = (it / kGtStages) & 1
+    for (int b = blockIdx.y; b < B; b += gridDim.y) {     // cluster-uniform
+        const char* g = reinterpret_cast<const char*>(gt_hwc + 3 * (size_t)b * npix);
+        float* xb = x_nchw + (size_t)b * C * (size_t)npix + (size_t)ch0 * (size_t)npix;
+        const int nunit = npix >> 2;
+        const int u0 = (int)((long long)nunit * rank / kGtCluster), u1 = (int)((long long)nunit * (rank + 1) / kGtCluster);
+        const int nchunk = (u1 - u0 + kGtChunkQuads - 1) / kGtChunkQuads;
+        auto issue = [&](int c, unsigned slot) {          // thread 0: chunk c of this slice -> ring stage `slot`
+            const int q0 = u0 + c * kGtChunkQuads;
+            const unsigned nq = (unsigned)min(kGtChunkQuads, u1 - q0);
+            bulk_load(s_in + (size_t)slot * (kGtChunkQuads * 3), g + 48 * (size_t)q0, nq * 48u, &s_full[slot]);
+        };
+        double sum = 0.0, sumsq = 0.0;
+        // ---- pass 1: statistics ----
+        if (tid == 0)
+            for (int c = 0; c < min(kGtStages, nchunk); ++c) issue(c, (it + c) % kGtStages);
+        for (int c = 0; c < nchunk; ++c, ++it) {
+            const unsigned slot = it % kGtStages;
+            mbar_wait(&s_full[slot], (it / kGtStages) & 1u);
+            const int q = u0 + c * kGtChunkQuads + tid;
+            if (q < u1) {
+                const float4* p = s_in + (size_t)slot * (kGtChunkQuads * 3) + 3 * tid;
+                const float4 a = p[0], cc = p[1], e = p[2];
+                const float s0 = ((a.x + a.y) + (a.z + a.w)) + ((cc.x + cc.y) + (cc.z + cc.w)) + ((e.x + e.y) + (e.z + e.w));
+                float s1 = fmaf(a.x, a.x, a.y * a.y) + fmaf(a.z, a.z, a.w * a.w);
+                s1 += fmaf(cc.x, cc.x, cc.y * cc.y) + fmaf(cc.z, cc.z, cc.w * cc.w);
+                s1 += fmaf(e.x, e.x, e.y * e.y) + fmaf(e.z, e.z, e.w * e.w);
+                sum += (double)s0; sumsq += (double)s1;
+            }
+            __syncthreads();              // the stage has been read by everyone
+            if (tid == 0 && c + kGtStages < nchunk) issue(c + kGtStages, slot);
+        }
+        sum = warp_sum(sum); sumsq = warp_sum(sumsq);
+        if (lane == 0) { s_warp[0][warp] = sum; s_warp[1][warp] = sumsq; }
+        __syncthreads();
+        if (tid == 0) {
+            double a = 0.0, c = 0.0;
+            for (int w = 0; w < kGtThreads / 32; ++w) { a += s_warp[0][w]; c += s_warp[1][w]; }
+            s_part[0] = a; s_part[1] = c;
+        }
+        cluster.sync();
+        if (tid == 0) {
+            double a = 0.0, c = 0.0;
+            for (int r = 0; r < kGtCluster; ++r) {
+                const double* rp = cluster.map_shared_rank(s_part, r);
+                a += rp[0]; c += rp[1];
+            }
+            const double cnt = 3.0 * (double)npix;          // ref: data_loaders.py:79-82 (population std, no zero guard)
+            const double mean = a / cnt;
+            double var = c / cnt - mean * mean;
+            if (var < 0.0) var = 0.0;
+            const double inv_std = 1.0 / sqrt(var);
+            s_aff[0] = (float)inv_std; s_aff[1] = (float)(-mean * inv_std);
+        }
+        cluster.sync();
+        const float sc = s_aff[0], of = s_aff[1];
+        // ---- pass 2: normalise + HWC -> CHW (the crop comes back from L2) ----
+        if (tid == 0)
+            for (int c = 0; c < min(kGtStages, nchunk); ++c) issue(c, (it + c) % kGtStages);
+        for (int c = 0; c < nchunk; ++c, ++it) {
+            const unsigned slot = it % kGtStages;
+            mbar_wait(&s_full[slot], (it / kGtStages) & 1u);
+            const int q0 = u0 + c * kGtChunkQuads;
+            const int nq = min(kGtChunkQuads, u1 - q0);
+            float4* ob = s_out + (size_t)(c & 1) * (3 * kGtChunkQuads);
+            if (tid < nq) {
+                const float4* p = s_in + (size_t)slot * (kGtChunkQuads * 3) + 3 * tid;
+                const float4 a = p[0], cc = p[1], e = p[2];
+                ob[tid] = make_float4(fmaf(a.x, sc, of), fmaf(a.w, sc, of), fmaf(cc.z, sc, of), fmaf(e.y, sc, of));
+                ob[kGtChunkQuads + tid] = make_float4(fmaf(a.y, sc, of), fmaf(cc.x, sc, of), fmaf(cc.w, sc, of), fmaf(e.z, sc, of));
+                ob[2 * kGtChunkQuads + tid] = make_float4(fmaf(a.z, sc, of), fmaf(cc.y, sc, of), fmaf(e.x, sc, of), fmaf(e.w, sc, of));
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // generic-proxy writes -> visible to the bulk store
+            __syncthreads();
+            if (tid == 0) {
+                for (int pl = 0; pl < 3; ++pl)
+                    bulk_store(xb + (size_t)pl * npix + 4 * (size_t)q0, ob + (size_t)pl * kGtChunkQuads, (unsigned)nq * 16u);
+                asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                // the OTHER output buffer (chunk c - 1) must have been read before chunk c + 1 overwrites it
+                asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                if (c + kGtStages < nchunk) issue(c + kGtStages, slot);
+            }
+            __syncthreads();
+        }
+        if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        __syncthreads();
+    }
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");      // all stores complete before the CTA exits
+}
+
+// RAC_GT_TMA=0 selects the register-staged kernel for standalone launches too (A/B measurements; default: bulk copies)
+static bool gt_tma_enabled() {
+    static const int v = [] { const char* e = getenv("RAC_GT_TMA"); return e ? atoi(e) : 1; }();
+    return v != 0;
+}
+
 // n_clusters: how many images are in flight at once (persistent clusters loop over the batch); <= 0 = one per image
 static int launch_gt_norm(const float* d_gt_hwc, float* d_x_nchw, int B, int npix, int use_norm_depth, int zero_render_planes,
                           int n_clusters, cudaStream_t stream, const unsigned* d_live_loads = nullptr, int W = 0, int ntx = 0, int nt = 0) {
@@ -354,6 +508,26 @@ static int launch_gt_norm(const float* d_gt_hwc, float* d_x_nchw, int B, int npi
     const int vec = (npix % 4 == 0 && (reinterpret_cast<uintptr_t>(d_gt_hwc) & 15u) == 0 &&
                      (reinterpret_cast<uintptr_t>(d_x_nchw) & 15u) == 0) ? 1 : 0;
     RAC_MAX_CARVEOUT_ONCE(gt_norm_kernel);     // (rac_assemble_input reaches this kernel without render_common)
+    // standalone launches (no zero-fill, one cluster per image, nothing co-resident): the bulk-copy variant
+    if (vec && !zero_render_planes && n_clusters <= 0 && !d_live_loads && gt_tma_enabled()) {
+        static std::atomic<int> configured{0};
+        if (!configured.load()) {
+            RAC_CUDA_CHECK(cudaFuncSetAttribute(gt_norm_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGtTmaSmem));
+            configured.store(1);
+        }
+        cudaLaunchConfig_t tc = {};
+        tc.gridDim = dim3(kGtCluster, B);
+        tc.blockDim = dim3(kGtThreads);
+        tc.dynamicSmemBytes = kGtTmaSmem;
+        tc.stream = stream;
+        cudaLaunchAttribute ta[1];
+        ta[0].id = cudaLaunchAttributeClusterDimension;
+        ta[0].val.clusterDim.x = kGtCluster; ta[0].val.clusterDim.y = 1; ta[0].val.clusterDim.z = 1;
+        tc.attrs = ta; tc.numAttrs = 1;
+        RAC_CUDA_CHECK(cudaLaunchKernelEx(&tc, gt_norm_tma_kernel, d_gt_hwc, d_x_nchw, npix, C, ch0, B));
+        RAC_LAUNCHED();
+        return RAC_OK;
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(kGtCluster, (n_clusters > 0 && n_clusters < B) ? n_clusters : B);
     cfg.blockDim = dim3(kGtThreads);

@@ -181,3 +181,37 @@ def test_first_sample_intrinsics_under_nccl_with_cpu_cam_mats(monkeypatch):
         assert rd.first_sample_intrinsics(Ks.cuda()) == (444.0, 333.0)
     finally:
         dist.destroy_process_group()
+
+
+def test_bulk_copy_gt_kernel_is_bit_identical_to_the_register_staged_one(tmp_path):
+    """gt_norm_tma_kernel (cp.async.bulk through a shared-memory ring; the standalone default) against gt_norm_kernel
+    (RAC_GT_TMA=0, read once per process: a child process) on ragged shapes: slices shorter than one 1024-px chunk, sizes
+    that are not a multiple of the chunk, B = 1, and the bench shape."""
+    import hashlib
+    import subprocess
+    import sys
+    script = tmp_path / "gt_variants.py"
+    script.write_text('''
+import hashlib, sys
+sys.path[:0] = %r
+import numpy as np, torch, rac
+from rac import render as R
+R.set_gt_cache(False)
+h = hashlib.sha1()
+for (B, H, W, use_depth) in [(1, 8, 12, False), (3, 40, 52, True), (5, 120, 160, False), (2, 240, 320, True), (9, 67, 100, False)]:
+    g = torch.Generator(device="cuda").manual_seed(B * 1000 + W)
+    init = torch.rand((B, H, W, 3), device="cuda", generator=g)
+    gt = torch.rand((B, H, W, 3), device="cuda", generator=g)
+    depth = torch.rand((B, H, W), device="cuda", generator=g) * 3
+    for rep in range(2):
+        x = rac.assemble_input_device(init, gt, depth if use_depth else None, use_depth)
+    h.update(x.cpu().numpy().tobytes())
+print(h.hexdigest())
+''' % (list(sys.path[:4]),))
+    import os
+    outs = {}
+    for tma in ("1", "0"):
+        r = subprocess.run([sys.executable, str(script)], capture_output=True, text=True, env=dict(os.environ, RAC_GT_TMA=tma))
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs[tma] = r.stdout.strip().splitlines()[-1]
+    assert outs["1"] == outs["0"], outs
