@@ -83,6 +83,23 @@ def make_inputs(seed):
     return mesh, sets, K
 
 
+STAGE_SOURCES = ["raster.cu", "raster.cuh", "raster_setup.inl", "raster_tile.inl", "raster_shade.inl", "raster_finalize.inl",
+                 "rac_common.cuh"]
+
+
+def stage_source_digest():
+    """sha256 (first 16 hex digits) over the sources of the rasterize+concat stage's kernels."""
+    import hashlib
+    h = hashlib.sha256()
+    try:
+        for name in STAGE_SOURCES:
+            with open(os.path.join(PKG, "csrc", name), "rb") as f:
+                h.update(f.read())
+    except OSError:
+        return None
+    return h.hexdigest()[:16]
+
+
 class ClockSampler(threading.Thread):
     """Samples SM clock + throttle reasons through NVML during the timed region."""
 
@@ -428,15 +445,10 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     # DRAM bytes per rac_render_concat call from the committed ncu capture of this same command — valid only for the
-    # kernels it was taken on: the capture records the digest of the library sources (build.py's stamp), and the field
-    # is null when the library in use was built from different sources.
+    # kernels it was taken on: the capture records a digest of the stage's kernel sources (stage_source_digest), and the
+    # field is null when the sources in the tree differ.
     traffic, traffic_rev, traffic_note = None, None, "no capture committed"
-    lib_digest = None
-    try:
-        with open(os.path.join(PKG, ".librac_b200.stamp")) as f:
-            lib_digest = f.read().strip()[:16]
-    except Exception:
-        pass
+    lib_digest = stage_source_digest()
     try:
         with open(os.path.join(ROOT, "profiles", "traffic_r02.json")) as f:
             tj = json.load(f)
@@ -446,7 +458,7 @@ def run_ours(args):
             traffic_note = ("profiles/traffic_r02.json: ncu dram__bytes_read+write summed over the stage's kernels, per call "
                             "(serialised capture, so part of the 118 MB written is still dirty in the 126 MB L2 when the last kernel ends)")
         else:
-            traffic_note = "profiles/traffic_r02.json was captured on library sources %s, this run uses %s: stale, not reported" % (traffic_rev, lib_digest)
+            traffic_note = "profiles/traffic_r02.json was captured on stage sources %s, this tree has %s: stale, not reported" % (traffic_rev, lib_digest)
     except Exception:
         pass
     achieved = algo_bytes / (stage_ms * 1e-3) / 1e9

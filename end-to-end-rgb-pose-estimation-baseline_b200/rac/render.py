@@ -298,15 +298,16 @@ def _host_staging(shape, dtype):
 
 
 def _pack_threads():
-    """Threads for the host pack: the cores this process may use, shared between the ranks of the node (torchrun
-    exports LOCAL_WORLD_SIZE), at most 16 — the pass is memory-bound."""
+    """Threads for the host pack: this process's fair share of the node's cores (torchrun exports LOCAL_WORLD_SIZE),
+    never more than its CPU affinity allows, at most 16 — the pass is memory-bound."""
     import os
+    total = os.cpu_count() or 1
     try:
-        cores = len(os.sched_getaffinity(0))
+        avail = len(os.sched_getaffinity(0))
     except Exception:
-        cores = os.cpu_count() or 1
+        avail = total
     ranks = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
-    return max(1, min(16, cores // ranks))
+    return max(1, min(16, avail, max(1, total // ranks)))
 
 
 def _pack_host_gt_u8(a):

@@ -167,3 +167,39 @@ def test_host_pack_recovers_png_codes_exactly():
             assert L.rac_host_pack_gt_u8(src.ctypes.data, 1, n, dst.ctypes.data, 0, ctypes.byref(ok)) == 0
             assert ok.value == 0, (n, bad)
     assert L.rac_host_pack_gt_u8(None, 1, 4, dst.ctypes.data, 0, ctypes.byref(ok)) < 0
+
+
+def test_host_pack_division_free_check_equals_the_division_form(monkeypatch):
+    """The FMA path accepts v iff |255 v - q| < 127.5 ulp(v) (no division); it must agree with the plain
+    `(double)q / 255.0 == v` form (RAC_PACK_NO_FMA=1) on every code, on the doubles next to every code, and on tiny /
+    signed-zero / out-of-range values."""
+    import ctypes
+    from rac import _lib
+    L = _lib.lib()
+    vals = []
+    for c in range(256):
+        t = c / 255.0
+        vals.append(t)
+        up = dn = t
+        for _ in range(4):
+            up, dn = np.nextafter(up, 2.0), np.nextafter(dn, -1.0)
+            vals += [up, dn]
+    vals += [5e-324, 1e-310, 1e-300, 2.0 ** -900, 2.0 ** -901, 1e-17, -0.0, 1.0 + 2 ** -52, np.nan, np.inf, -np.inf]
+    ok = ctypes.c_int(-1)
+    dst = np.empty(70000, np.uint8)
+    verdicts = {}
+    for no_fma in ("0", "1"):
+        if no_fma == "1":
+            monkeypatch.setenv("RAC_PACK_NO_FMA", "1")
+        else:
+            monkeypatch.delenv("RAC_PACK_NO_FMA", raising=False)
+        out = []
+        for v in vals:
+            a = np.full(70000, 100 / 255.0)
+            a[12345] = v
+            assert L.rac_host_pack_gt_u8(a.ctypes.data, 1, a.size, dst.ctypes.data, 2, ctypes.byref(ok)) == 0
+            out.append(ok.value)
+        verdicts[no_fma] = out
+    assert verdicts["0"] == verdicts["1"]
+    want = [int(any(v == c / 255.0 for c in range(256))) for v in vals]
+    assert verdicts["1"] == want
