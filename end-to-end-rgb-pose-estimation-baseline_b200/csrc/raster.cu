@@ -3,21 +3,26 @@
 // Replaces: data_loaders.py:84-118 (render_batch) -> renderer.py:85-105 (render_scene) ->
 // pyrender/OpenGL (R1-R9 in SURVEY.md §8a), and data_loaders.py:158-177 (prepare_model_input).
 //
-// Three kernels per call (see raster.cuh for the spec they implement):
-//   setup_kernel     (raster_setup.inl) one thread per (image, triangle): transform, project, snap, cull,
-//                    1/z plane, camera-frame normal -> TriRec.  The CTA (256 triangles of one image) bins
-//                    its survivors by 32x16-px tile in shared memory and publishes, without any global
-//                    atomic, a private ref region (u8 local ids grouped by tile) plus one descriptor per
-//                    tile.  Triangles spanning more than 2x2 tiles go to a per-image large list.
-//   raster_kernel    (raster_tile.inl, raster_shade.inl) one CTA per (image, tile): the tile's 4x-MSAA
-//                    visibility buffer (depth24 | triangle id, 8 B per sample, 16 KB) lives in shared
-//                    memory; the tile's triangles are gathered through the descriptors and scattered into
-//                    it with shared-memory atomic-min (exact int32 edge functions for binned triangles,
-//                    int64 for large ones); then every pixel is shaded + resolved once and written as
-//                    RGBA8 + f32 depth; per-image max / mean / std accumulators are reduced per CTA and
+// Kernels of one call (see raster.cuh for the spec they implement):
+//   setup_kernel     (raster_setup.inl) 128 threads x 2 triangles of one image: transform, project, snap, cull, 1/z
+//                    plane, camera-frame normal -> 48-B record.  The CTA bins its survivors by 32x16-px bin in shared
+//                    memory and publishes, without any global atomic, a private ref region (u8 local ids grouped by
+//                    bin) plus one descriptor per bin; triangles spanning more than 2x2 bins — or whose UNCLIPPED extent
+//                    exceeds 64 px — go to a per-image large list (int64 edge functions).  The CTA that finishes an
+//                    image last appends the image's non-empty bins to 16 load-class lists.
+//   raster_kernel    (raster_tile.inl, raster_shade.inl) persistent CTAs (SMs x resident CTAs) pop bins heaviest class
+//                    first; every ticket comes from one atomic counter.  Per bin the 4x-MSAA visibility buffer lives in
+//                    shared memory as 32-bit keys (depth24 << 8 | batch-local triangle id, 8 KB): triangles are
+//                    gathered through the descriptors and scattered into it with ONE native shared-memory atomic-min per
+//                    covered sample (exact int32 edge functions for binned triangles, int64 for large ones); more than
+//                    254 triangles in a bin commit (shade + park) between batches.  Then every pixel is shaded + resolved
+//                    once and written as RGBA8 + f32 depth; per-image max / depth statistics are reduced per CTA and
 //                    flushed with atomics.
-//   finalize_*       (raster_finalize.inl) streaming pass: RGBA8+depth (L2-resident) [+ gt crop] ->
-//                    normalised f32 outputs with 128-bit coalesced stores (NCHW concat or HWC render).
+//   gt_norm_kernel   (raster_finalize.inl) on a forked stream, resident next to the raster CTAs: zero background of the
+//                    render planes + normalised gt planes of x (8-CTA cluster per image, DSMEM reduction).
+//   finalize_live_kernel  non-empty bins only: RGBA8 + depth (L2-resident) -> normalised f32 outputs with 128-bit
+//                    coalesced stores (NCHW concat or HWC render).
+//   gt_norm_tma_kernel / assemble_render_kernel / depth_stats_kernel: rac_assemble_input (existing renders).
 #include "raster.cuh"
 #include <cooperative_groups.h>
 #include <mutex>
