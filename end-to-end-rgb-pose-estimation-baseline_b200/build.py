@@ -14,8 +14,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librac_b200.so")
 STAMP = os.path.join(HERE, ".librac_b200.stamp")
-SOURCES = ["rac_api.cu", "raster.cu", "pose_update.cu", "add_loss.cu", "aux_kernels.cu", "host_pack.cu"]
-HEADERS = ["rac_common.cuh", "raster.cuh", "raster_setup.inl", "raster_shade.inl", "raster_tile.inl", "raster_finalize.inl",
+SOURCES = ["rac_api.cu", "raster.cu", "pose_update.cu", "add_loss.cu", "aux_kernels.cu", "host_pack.cu", "pose_loss_step.cu"]
+HEADERS = ["rac_common.cuh", "pose_update_dev.cuh", "add_loss_dev.cuh", "raster.cuh", "raster_setup.inl", "raster_shade.inl", "raster_tile.inl", "raster_finalize.inl",
            os.path.join("..", "..", "include", "rac.h")]
 
 NVCC_FLAGS = [

@@ -60,6 +60,8 @@ SIGNATURES = {
     "rac_add_loss_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p,
                                  c_void_p, c_void_p, c_void_p, c_void_p]),
     "rac_add_loss_bwd": (c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "rac_pose_loss_step": (c_int, [c_void_p, c_int, c_void_p, c_int, ctypes.c_double, ctypes.c_double, c_void_p, c_void_p, c_void_p,
+                                   c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "rac_transform_pts_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "rac_transform_pts_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "rac_sample_poses": (c_int, [c_void_p, c_void_p, c_int, c_double, c_double, c_double, c_double, c_double,

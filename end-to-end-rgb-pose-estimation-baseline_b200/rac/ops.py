@@ -170,3 +170,36 @@ def rot_id(rot_repr):
     if rot_repr not in RAC_ROT:
         assert False   # ref: rotation_representation.py:157
     return RAC_ROT[rot_repr]
+
+
+_LOSS_SLOT = {   # loss name -> (mode, pred_is_a): which argument slot of the loss the NEW pose takes in the drivers' calls
+    "add_l1": (_lib.LOSS_ADD_L1, 0),                     # compute_ADD_L1_loss(T_gt, T_new)            train_model.py:246
+    "add_l2": (_lib.LOSS_ADD_L2, 0),                     # compute_ADD_L2_loss(T_gt, T_new)
+    "add_l1_disentangled": (_lib.LOSS_DISENTANGLED, 0),  # compute_disentangled_ADD_L1_loss(T_gt, T_new)  :280 (swapped, Q7)
+    "add_l1_disentl_scaled": (_lib.LOSS_DISENT_SCALED, 1),   # compute_scaled_disentl_ADD_L1_loss(T_prev, T_new, T_gt)  :283
+}
+
+
+def pose_loss_step(y, T_in, rot_repr, fx, fy, T_gt, pts, loss_name, T_prev=None, out=None, feedback=None):
+    """calculate_T_CO_pred + loss + batch mean + backward to y in ONE launch (rac_pose_loss_step), for callers that own
+    their loop.  y (B,D), T_in (B,4,4) f32/f64, T_gt (B,4,4), pts (B,N,3), all CUDA.  -> (T_new, loss (1,), grad_y,
+    per_sample); `out` may hand in preallocated (T_new, loss, grad_y, per_sample) tensors (CUDA-graph capture);
+    `feedback` (B,4,4) f32 also receives T_new and may be T_in / T_prev themselves (the loop's T_CO_pred = T_CO_pred_new)."""
+    L = _lib.lib()
+    mode, pred_is_a = _LOSS_SLOT[loss_name]
+    yy = _cu(y)
+    t64 = T_in.dtype == torch.float64
+    Ti = _cu(T_in, torch.float64 if t64 else torch.float32)
+    Tg, P = _cu(T_gt), _cu(pts)
+    Tp = _cu(T_prev) if T_prev is not None else None
+    B, N = P.shape[0], P.shape[1]
+    assert yy.shape[0] == B and tuple(Ti.shape) == (B, 4, 4) and tuple(Tg.shape) == (B, 4, 4) and P.shape[2] == 3
+    dev = yy.device
+    if out is None:
+        out = (torch.empty((B, 4, 4), dtype=torch.float32, device=dev), torch.empty(1, dtype=torch.float32, device=dev),
+               torch.empty_like(yy), torch.empty(B, dtype=torch.float32, device=dev))
+    T_new, loss, grad_y, per = out
+    _lib.check(L.rac_pose_loss_step(_lib.ptr(yy), RAC_ROT[rot_repr], _lib.ptr(Ti), int(t64), float(fx), float(fy), _lib.ptr(Tg),
+                                    _lib.ptr(Tp), _lib.ptr(P), B, N, mode, pred_is_a, _lib.ptr(T_new), _lib.ptr(per), _lib.ptr(loss),
+                                    _lib.ptr(grad_y), _lib.ptr(feedback), _lib.ptr(_counter(dev)), _lib.stream_ptr()))
+    return T_new, loss, grad_y, per

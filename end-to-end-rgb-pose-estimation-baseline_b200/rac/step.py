@@ -32,7 +32,7 @@ _LOSSES = ("add_l1", "add_l2", "add_l1_disentangled", "add_l1_disentl_scaled")
 
 class RenderCompareStep:
     def __init__(self, meshes, B, img_size, rot_repr="6D", loss="add_l1_disentangled", n_points=1000,
-                 use_norm_depth=False, fx=None, fy=None, device=None):
+                 use_norm_depth=False, fx=None, fy=None, device=None, fused_pose_loss=True):
         import loss as L                       # the shadow modules (reference signatures)
         import rotation_representation as RR
         assert loss in _LOSSES, loss
@@ -58,6 +58,10 @@ class RenderCompareStep:
         self.grad_y = torch.zeros((B, D), **f32)
         self._fx, self._fy = fx, fy
         self._L, self._RR = L, RR
+        # the post-CNN half as ONE launch (rac_pose_loss_step) instead of the four kernels behind the reference-named
+        # functions; False keeps the reference-named path (what the drivers call) for parity tests
+        self.fused_pose_loss = bool(fused_pose_loss)
+        self._per_sample = torch.empty(B, **f32)
         self._g_all = self._g_render = self._g_pose = self._g_chain = None
 
     # ---- the eager bodies (also what gets captured) ----
@@ -65,7 +69,19 @@ class RenderCompareStep:
         render_concat_device(self.T_pred, self.meshes, self.K, (self.W, self.H), self.gt,
                              use_norm_depth=self.use_norm_depth, out=self.x)
 
-    def _pose_loss(self):
+    def _pose_loss(self, feed_back=False):
+        """feed_back (chain mode): T_pred <- T_new inside the same launch; the scaled loss then reads the iteration's
+        input pose from T_pred itself (train_model.py:283 passes T_CO_pred), so T_prev needs no copy either."""
+        if self.fused_pose_loss:
+            from .ops import pose_loss_step
+            K0 = self._Ks_host[0]
+            scaled = self.loss_name == "add_l1_disentl_scaled"
+            pose_loss_step(self.y, self.T_pred, self.rot_repr, float(K0[0, 0]), float(K0[1, 1]), self.T_gt, self.pts, self.loss_name,
+                           T_prev=(self.T_pred if feed_back else self.T_prev) if scaled else None,
+                           out=(self.T_new, self.loss, self.grad_y, self._per_sample), feedback=self.T_pred if feed_back else None)
+            if feed_back and scaled:
+                self.T_prev.copy_(self.T_new)      # keep the public T_prev buffer coherent for a caller that reads it
+            return
         L, RR = self._L, self._RR
         y = self.y.detach().requires_grad_(True)
         Ks = self._Ks_host
@@ -122,9 +138,12 @@ class RenderCompareStep:
         n0 = _lib.launch_count()
         with torch.cuda.graph(self._g_chain):
             self._render()
-            self._pose_loss()
-            self.T_pred.copy_(self.T_new)                    # train_model.py:250: the next iteration renders under T_new
-            self.T_prev.copy_(self.T_new)                    # (the scaled loss reads the iteration's input pose, train_model.py:283)
+            if self.fused_pose_loss:
+                self._pose_loss(feed_back=True)              # T_pred <- T_new inside the launch (train_model.py:250)
+            else:
+                self._pose_loss()
+                self.T_pred.copy_(self.T_new)                # train_model.py:250: the next iteration renders under T_new
+                self.T_prev.copy_(self.T_new)                # (the scaled loss reads the iteration's input pose, train_model.py:283)
         self.launches_per_chain = _lib.launch_count() - n0
         return self
 

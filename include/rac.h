@@ -190,6 +190,21 @@ RAC_API int rac_add_loss_fwd(const float* d_T_a, const float* d_T_b, const float
 /* g_T[b] = d_w[b] * d_grad[b] (w = upstream gradient per sample); out (B,4,4). */
 RAC_API int rac_add_loss_bwd(const float* d_grad, const float* d_w, int B, float* d_gT, rac_stream_t stream);
 
+/* The whole post-CNN half of one refinement iteration in one launch, for callers that own their loop
+ * (rac.RenderCompareStep): ref train_model.py:245-247,276-285 / test_model.py:101-103 — calculate_T_CO_pred, the loss,
+ * its batch mean and backward down to the CNN's output.  d_y (B,D) head output; d_T_in (B,4,4) f32 or f64 (Q6);
+ * d_T_gt (B,4,4); d_T_prev (B,4,4) for RAC_LOSS_DISENT_SCALED, else NULL; d_pts (B,N,3).
+ * pred_is_a: which argument slot of rac_add_loss_fwd the NEW pose takes (0: T_a = T_gt, T_b = T_new — ADD-L1/L2 and the
+ * disentangled loss in train_model.py:280's swapped order; 1: T_a = T_new, T_b = T_gt — the scaled loss, loss.py:101).
+ * Outputs: d_T_new (B,4,4), d_per_sample (B), d_mean (1, nullable), d_grad_y (B,D) = d(mean loss)/d(y);
+ * d_T_feedback (B,4,4, nullable): T_new is stored there as well — the loop's `T_CO_pred = T_CO_pred_new`
+ * (train_model.py:250); it MAY alias an f32 d_T_in and d_T_prev (the old pose is read before it is overwritten).
+ * Same per-sample arithmetic as the four stand-alone launches.  d_counter: as for rac_add_loss_fwd. */
+RAC_API int rac_pose_loss_step(const float* d_y, int rot_repr, const void* d_T_in, int t_in_is_f64, double fx, double fy,
+                               const float* d_T_gt, const float* d_T_prev, const float* d_pts, int B, int N,
+                               int loss_mode, int pred_is_a, float* d_T_new, float* d_per_sample, float* d_mean,
+                               float* d_grad_y, float* d_T_feedback, unsigned int* d_counter, rac_stream_t stream);
+
 /* ref: loss.py:60-78 (transform_pts): d_T (B,M,4,4) (M = 1 for the 3-dim case),
  * d_pts (B,N,3) -> d_out (B,M,N,3). */
 RAC_API int rac_transform_pts_fwd(const float* d_T, const float* d_pts, int B, int M, int N,

@@ -40,7 +40,7 @@ def test_graph_step_matches_eager_and_oracle(rot, loss, C7):
     for t in (st.x, st.T_new, st.loss, st.grad_y):
         t.zero_()
     st.capture()
-    assert st.launches_per_run >= 7
+    assert st.launches_per_run >= 5            # setup, gt_norm, raster, finalize_live + the fused pose/loss step
     for _ in range(3):                       # replays must be idempotent
         st.run()
     torch.cuda.synchronize()
@@ -143,3 +143,76 @@ def test_mixed_mesh_step_is_capturable():
     _, _, rgba_o = ro.render_batch_mixed(batch, T, K, (W, H))
     cov = (st.x[:, :3].abs().sum(1) > 0).cpu().numpy()             # any sample covered (resolved colour > 0)
     assert ((cov != (rgba_o[..., :3].max(-1) > 0)).reshape(B, -1).sum(1) <= 0.002 * W * H).all()
+
+
+@pytest.mark.parametrize("rot", ["6D", "SVD", "3D"])
+@pytest.mark.parametrize("loss", ["add_l1", "add_l2", "add_l1_disentangled", "add_l1_disentl_scaled"])
+def test_fused_pose_loss_step_equals_the_reference_named_calls(rot, loss):
+    """rac_pose_loss_step (one launch: pose update + loss + batch mean + backward to y) against the four launches behind
+    calculate_T_CO_pred / compute_*_loss / backward that the drivers use — same per-sample device code, so the results
+    agree to the last bits; f32 and f64 (Q6) input poses, ragged B and N."""
+    import loss as L
+    import rotation_representation as RR
+    from rac.ops import pose_loss_step
+    rng = np.random.default_rng(hash((rot, loss)) % 2 ** 31)
+    B, N = 37, 333
+    D = {"6D": 9, "SVD": 12, "3D": 6}[rot]
+    T, Tg = sample_poses(B, seed=3)
+    y = (0.2 * rng.normal(size=(B, D))).astype(np.float32)
+    if rot != "3D":
+        y[:, 0] += 1; y[:, 4] += 1
+    if rot == "SVD":
+        y[:, 8] += 1
+    y[:, -1] = 1.0 + 0.05 * rng.normal(size=B)
+    K = torch.tensor(intrinsics(B, 320, 240))
+    pts = torch.tensor(rng.normal(size=(B, N, 3)).astype(np.float32) * 0.3, device="cuda")
+    T_gt = torch.tensor(Tg, device="cuda")
+    for dtype in (torch.float32, torch.float64):
+        T_in = torch.tensor(T, device="cuda").to(dtype)
+        T_prev = torch.tensor(T, device="cuda")
+        yg = torch.tensor(y, device="cuda", requires_grad=True)
+        T_new = RR.calculate_T_CO_pred(yg, T_in, rot, K)
+        if loss == "add_l1":
+            l = L.compute_ADD_L1_loss(T_gt, T_new, pts)
+        elif loss == "add_l2":
+            import contextlib, io
+            with contextlib.redirect_stdout(io.StringIO()):
+                l = L.compute_ADD_L2_loss(T_gt, T_new, pts)
+        elif loss == "add_l1_disentangled":
+            l = L.compute_disentangled_ADD_L1_loss(T_gt, T_new, pts)             # train_model.py:280 order
+        else:
+            l = L.compute_scaled_disentl_ADD_L1_loss(T_prev, T_new, T_gt, pts)
+        l.backward()
+        Tn, lf, gy, per = pose_loss_step(torch.tensor(y, device="cuda"), T_in, rot, float(K[0, 0, 0]), float(K[0, 1, 1]), T_gt, pts, loss,
+                                         T_prev=T_prev if loss == "add_l1_disentl_scaled" else None)
+        torch.cuda.synchronize()
+        assert torch.equal(Tn, T_new.detach()), (rot, loss, dtype)
+        np.testing.assert_allclose(lf.item(), l.item(), rtol=1e-6)
+        np.testing.assert_allclose(gy.cpu().numpy(), yg.grad.cpu().numpy(), rtol=2e-5, atol=1e-8)
+        assert per.shape == (B,) and np.isclose(per.mean().item(), l.item(), rtol=1e-5)
+
+
+def test_step_reference_named_path_still_matches_the_fused_one():
+    import rac
+    from rac import mesh as M
+    m = M.bumpy_sphere(level=3, seed=4)
+    B, W, H, N = 5, 160, 120, 200
+    rng = np.random.default_rng(2)
+    T, Tg = sample_poses(B, seed=8)
+    outs = []
+    for fused in (True, False):
+        st = rac.RenderCompareStep(m, B, (W, H), rot_repr="SVD", loss="add_l1_disentl_scaled", n_points=N, fused_pose_loss=fused)
+        r = np.random.default_rng(2)
+        y = (0.1 * r.normal(size=(B, 12))).astype(np.float32); y[:, 0] += 1; y[:, 4] += 1; y[:, 8] += 1; y[:, -1] = 1.0
+        st.T_pred.copy_(torch.tensor(T)); st.T_prev.copy_(torch.tensor(T)); st.K.copy_(torch.tensor(intrinsics(B, W, H)))
+        st.gt.copy_(torch.tensor(r.uniform(0, 1, (B, H, W, 3)).astype(np.float32))); st.y.copy_(torch.tensor(y))
+        st.T_gt.copy_(torch.tensor(Tg)); st.pts.copy_(torch.tensor(m.verts[r.integers(0, len(m.verts), (B, N))]))
+        st.capture()
+        st.T_pred.copy_(torch.tensor(T)); st.T_prev.copy_(torch.tensor(T))
+        for _ in range(3):
+            st.run_chain()
+        torch.cuda.synchronize()
+        outs.append([t.clone() for t in (st.x, st.T_pred, st.loss, st.grad_y)])
+    assert torch.equal(outs[0][1], outs[1][1]) and torch.equal(outs[0][0], outs[1][0])
+    np.testing.assert_allclose(outs[0][2].item(), outs[1][2].item(), rtol=1e-6)
+    np.testing.assert_allclose(outs[0][3].cpu().numpy(), outs[1][3].cpu().numpy(), rtol=2e-5, atol=1e-8)
