@@ -10,7 +10,7 @@ PKG = os.path.join(ROOT, "end-to-end-rgb-pose-estimation-baseline_b200")
 OUT = os.path.join(PKG, "librac_b200_timing.so")
 sys.path[:0] = [PKG, ROOT]
 
-CASES = [(0, "all (side work first: 1 gt CTA/SM resident)"), (32, "all, setup launched first"), (64, "all, gt kernel one cluster per image"),
+CASES = [(0, "all (product order: gt kernel forked after setup)"), (32, "all, gt kernel forked BEFORE setup"), (64, "all, gt kernel one cluster per image"),
          (16, "side work on the main stream (no fork)"),
          (1, "no side work"), (8, "no finalize"), (9, "no side work, no finalize"),
          (13 + 16, "setup only"), (14 + 16, "side work only"), (14 + 16 + 64, "side work only, cluster per image"), (15 + 16, "memset only")]
