@@ -16,11 +16,14 @@ _ws_cache = {}
 
 
 def _workspace(dev, nbytes):
-    """Grow-only per-device scratch.  Reuse is stream-ordered: every kernel of a call is enqueued on
+    """Grow-only scratch per (device, stream), at most 8 of them.  Reuse is stream-ordered: every kernel of a call is enqueued on
     the current stream, so a later call on the same stream cannot overtake an earlier one."""
     key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:
+        if ws is None:
+            while len(_ws_cache) >= 8:      # short-lived streams (one per captured graph, say) must not pin a workspace each forever
+                _ws_cache.pop(next(iter(_ws_cache)))
         ws = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=dev)
         _ws_cache[key] = ws
     return ws
@@ -168,6 +171,8 @@ def _gt_staging(dev, shape, dtype=torch.float32):
     key = (dev.index, tuple(shape), dtype)
     ring = _gt_rings.get(key)
     if ring is None:
+        while len(_gt_rings) >= 4:          # bounded like the pinned rings (the caching allocator reuses the freed blocks)
+            _gt_rings.pop(next(iter(_gt_rings)))
         ring = {"next": 0, "bufs": [None] * _GT_RING, "done": [None] * _GT_RING}
         _gt_rings[key] = ring
     i = ring["next"]
@@ -280,12 +285,18 @@ def _gt_cache_store(t, dev, planes):
 # asynchronous and runs at full PCIe rate.  A ring slot is reused only after the copy that read it has completed.
 _host_rings = {}
 _HOST_RING = 2
+_MAX_STAGING_SHAPES = 4
 
 
 def _host_staging(shape, dtype):
     key = (tuple(shape), dtype)
     ring = _host_rings.get(key)
     if ring is None:
+        while len(_host_rings) >= _MAX_STAGING_SHAPES:      # ragged last batches bring new shapes: keep pinned memory bounded
+            old = _host_rings.pop(next(iter(_host_rings)))
+            for ev in old["ev"]:
+                if ev is not None:
+                    ev.synchronize()
         ring = {"next": 0, "bufs": [None] * _HOST_RING, "ev": [None] * _HOST_RING}
         _host_rings[key] = ring
     i = ring["next"]
