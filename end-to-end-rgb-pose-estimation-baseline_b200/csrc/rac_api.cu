@@ -195,6 +195,7 @@ static int mesh_create_common(const float* h_verts, int V, const int32_t* h_face
         q.alpha2 = alpha * alpha;
         q.kgeo = (rough + 1.0f) * (rough + 1.0f) * 0.125f;
         q.has_vcolor = parts[k].use_vertex_color ? 1 : 0;
+        q.double_sided = parts[k].double_sided ? 1 : 0;
         if (parts[k].tex_rgb8) {
             q.tex = (const uchar4*)(blk + o_tex) + part_mip_off[k];
             q.tw = parts[k].tex_w; q.th = parts[k].tex_h; q.nmips = part_nmips[k];

@@ -66,7 +66,8 @@ struct PartDev {
     float metallic, alpha2, kgeo;   // alpha2 = roughness^4, kgeo = (roughness + 1)^2 / 8 (roughness clamped to [0.04, 1])
     int has_vcolor;                 // COLOR_0 applies to this part (parts without a material, pyrender's default one)
     const uchar4* tex;              // this part's mip chain, or nullptr
-    int tw, th, nmips, pad;
+    int tw, th, nmips;
+    int double_sided;               // glTF doubleSided: back faces are drawn too (unlit side: the normal is not flipped)
 };
 
 struct MeshDev {

@@ -127,9 +127,11 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
             keep[k] = keep[k] && project_vertex(cam, mesh.verts + 3 * (size_t)i2, znear, X2, Y2, iz2);
         }
         long long area2 = 0;
+        bool back = false;         // a back face that is drawn anyway: its part's material is doubleSided (multi-part meshes only)
         if (keep[k]) {
             area2 = (long long)(X1 - X0) * (Y2 - Y0) - (long long)(X2 - X0) * (Y1 - Y0);
-            keep[k] = area2 < 0;   // RS-T: front faces have negative area in (u, v-down) image coordinates
+            if (area2 > 0 && mesh.parts) back = mesh.parts[mesh.face_part[t]].double_sided != 0;
+            keep[k] = area2 < 0 || back;   // RS-T: front faces have negative area in (u, v-down) image coordinates
         }
         if (keep[k]) {
             // pixels that own at least one sample inside the bounding box (sample offsets span 32..224)
@@ -144,17 +146,23 @@ setup_body(const MeshDev* __restrict__ table, const int* __restrict__ mesh_ids, 
             tx0[k] = px0 / kTileW; tx1[k] = px1 / kTileW; ty0[k] = py0 / kTileH; ty1[k] = py1 / kTileH;
         }
         if (keep[k]) {
-            // swap v1 <-> v2 so that the interior is on the non-negative side of all three edges
-            int sx = X1, sy = Y1; X1 = X2; Y1 = Y2; X2 = sx; Y2 = sy;
-            float tz = iz1; iz1 = iz2; iz2 = tz;
-            const float areaf = (float)(-area2);
+            // swap v1 <-> v2 so that the interior is on the non-negative side of all three edges (a drawn back face
+            // already has it there)
+            if (!back) {
+                int sx = X1, sy = Y1; X1 = X2; Y1 = Y2; X2 = sx; Y2 = sy;
+                float tz = iz1; iz1 = iz2; iz2 = tz;
+            }
+            const float areaf = (float)(back ? area2 : -area2);
             const float d1 = __fsub_rn(iz1, iz0), d2 = __fsub_rn(iz2, iz0);
             const float ex1 = (float)(X1 - X0), ey1 = (float)(Y1 - Y0);
             const float ex2 = (float)(X2 - X0), ey2 = (float)(Y2 - Y0);
             const float gx = __fdiv_rn(__fmaf_rn(d1, ey2, -__fmul_rn(d2, ey1)), areaf);
             const float gy = __fdiv_rn(__fmaf_rn(d2, ex1, -__fmul_rn(d1, ex2)), areaf);
             const float* fn = mesh.fnormals + 3 * (size_t)t;
-            const float nx = cam.r[0] * fn[0] + cam.r[1] * fn[1] + cam.r[2] * fn[2];
+            float nx = cam.r[0] * fn[0] + cam.r[1] * fn[1] + cam.r[2] * fn[2];
+            // multi-part meshes: the lowest mantissa bit of nx tells the shader whether the record keeps the mesh's vertex
+            // order (1: drawn back face) or the swapped one (0) — it picks the attribute indices accordingly
+            if (mesh.parts) nx = __uint_as_float((__float_as_uint(nx) & ~1u) | (back ? 1u : 0u));
             const float ny = cam.r[3] * fn[0] + cam.r[4] * fn[1] + cam.r[5] * fn[2];
             const float nz = cam.r[6] * fn[0] + cam.r[7] * fn[1] + cam.r[8] * fn[2];
             int4* r = recs + 3 * ((size_t)b * maxT + t);

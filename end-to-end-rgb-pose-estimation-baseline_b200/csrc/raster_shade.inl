@@ -100,8 +100,10 @@ __device__ __noinline__ void shade_base_color(const ShadeCtx& sc, const int4* __
         float w[3], wxv[3], wyv[3];
         persp_bary<true>(g, Pcx, Pcy, w, wxv, wyv);
         const float w0 = w[0], w1 = w[1], w2 = w[2];
-        // record order is (v0, v2, v1) of the mesh face (setup swaps v1 <-> v2)
-        const int i0 = sc.faces[3 * tri], i1 = sc.faces[3 * tri + 2], i2 = sc.faces[3 * tri + 1];
+        // record order is (v0, v2, v1) of the mesh face (setup swaps v1 <-> v2) — except for the drawn back faces of a
+        // doubleSided part, which keep the mesh order (flag: lowest mantissa bit of the record's nx, multi-part meshes only)
+        const bool mesh_order = sc.parts && (rec[2].y & 1);
+        const int i0 = sc.faces[3 * tri], i1 = sc.faces[3 * tri + (mesh_order ? 1 : 2)], i2 = sc.faces[3 * tri + (mesh_order ? 2 : 1)];
         // multi-part meshes: the face's own texture; COLOR_0 only where the part asks for it
         const uchar4* tex = sc.tex;
         int tw = sc.tw, th = sc.th, nmips = sc.nmips;

@@ -23,7 +23,7 @@ class RacMaterial(ctypes.Structure):
 
 class RacPart(ctypes.Structure):
     _fields_ = [("material", RacMaterial), ("tex_rgb8", c_void_p), ("tex_w", c_int), ("tex_h", c_int),
-                ("use_vertex_color", c_int)]
+                ("use_vertex_color", c_int), ("double_sided", c_int)]
 
 
 class RacScene(ctypes.Structure):

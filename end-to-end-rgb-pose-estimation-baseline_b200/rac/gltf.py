@@ -16,8 +16,11 @@ Material mapping (trimesh PBRMaterial -> pyrender MetallicRoughnessMaterial, pyr
     a primitive WITHOUT a material gets pyrender's default material (0.3 grey, metallic 0.2, roughness 0.8) and, if it
     carries COLOR_0, vertex colours; COLOR_0 of a primitive WITH a material is ignored (trimesh parks it in
     vertex_attributes, pyrender never sees it).
+    material.doubleSided (what Blender writes unless "backface culling" is ticked): the part's back faces are drawn too —
+    pyrender switches GL_CULL_FACE off for such a material and its mesh.frag does not flip the normal, so they receive
+    ambient light only.
 Not applied (documented in DESIGN.md §7): normal / occlusion / emissive / metallicRoughness textures, alpha blending,
-doubleSided (back faces are culled for every material), KHR extensions, sparse accessors, non-triangle primitives.
+KHR extensions, sparse accessors, non-triangle primitives.
 No third-party parser: struct + json + PIL for the embedded PNG / JPEG images.
 """
 import io
@@ -92,7 +95,7 @@ def _material(gltf, binary, idx):
     if "baseColorTexture" in pbr:
         tex = _image_rgb(gltf, binary, pbr["baseColorTexture"]["index"])
     return {"material": (bc[0], bc[1], bc[2], bc[3], float(pbr.get("metallicFactor", 1.0)), float(pbr.get("roughnessFactor", 1.0))),
-            "tex": tex}
+            "tex": tex, "double_sided": bool(m.get("doubleSided", False))}
 
 
 def load_glb(path, apply_rx90=True):
@@ -123,7 +126,7 @@ def load_glb(path, apply_rx90=True):
                     mat_cache[prim["material"]] = _material(gltf, binary, prim["material"])
                 part = dict(mat_cache[prim["material"]], use_vcolor=False)
             else:
-                part = {"material": DEFAULT_MATERIAL, "tex": None, "use_vcolor": "COLOR_0" in attr}
+                part = {"material": DEFAULT_MATERIAL, "tex": None, "use_vcolor": "COLOR_0" in attr, "double_sided": False}
             uv = np.zeros((len(pos), 2), dtype=np.float32)
             if has_mat and "TEXCOORD_0" in attr:
                 uv = _accessor(gltf, binary, attr["TEXCOORD_0"]).astype(np.float32)[:, :2]
@@ -151,7 +154,8 @@ def load_glb(path, apply_rx90=True):
 
 # ---- writer (tests and synthetic "texturized" datasets) ------------------------------------------------------------
 def save_glb(path, prims, node_translation=None):
-    """prims: list of dict(verts (V,3), faces (T,3), uv (V,2)?, vcolor (V,4) u8?, material (6,)? , tex RGB8 (h,w,3)?).
+    """prims: list of dict(verts (V,3), faces (T,3), uv (V,2)?, vcolor (V,4) u8?, material (6,)? , tex RGB8 (h,w,3)?,
+    double_sided bool?).
     One glTF mesh with one primitive per entry, each with its own material when `material` / `tex` is given; images are
     embedded as PNG.  node_translation: a node transform that a faithful loader must IGNORE (the reference iterates
     scene.geometry, not the scene graph)."""
@@ -196,7 +200,7 @@ def save_glb(path, prims, node_translation=None):
                 images.append({"bufferView": add_view(buf.getvalue()), "mimeType": "image/png"})
                 textures.append({"source": len(images) - 1})
                 pbr["baseColorTexture"] = {"index": len(textures) - 1}
-            materials.append({"pbrMetallicRoughness": pbr, "doubleSided": False})
+            materials.append({"pbrMetallicRoughness": pbr, "doubleSided": bool(p.get("double_sided", False))})
             prim["material"] = len(materials) - 1
         gprims.append(prim)
     node = {"mesh": 0}

@@ -327,6 +327,7 @@ class DeviceMesh:
                     arr[k].material.base_color[i] = float(m[i])
                 arr[k].material.metallic, arr[k].material.roughness = float(m[4]), float(m[5])
                 arr[k].use_vertex_color = int(bool(p.get("use_vcolor", False)))
+                arr[k].double_sided = int(bool(p.get("double_sided", False)))
                 tex = p.get("tex")
                 if tex is not None and mesh.uv is not None:
                     tex = np.ascontiguousarray(tex, dtype=np.uint8)

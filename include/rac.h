@@ -103,6 +103,8 @@ typedef struct rac_part {
     const uint8_t* tex_rgb8;    /* (tex_h, tex_w, 3) or NULL */
     int tex_w, tex_h;
     int use_vertex_color;
+    int double_sided;           /* glTF material.doubleSided: no back-face culling for this part; back faces keep the
+                                   geometric normal (pyrender's mesh.frag does not flip it), so they show ambient light only */
 } rac_part_t;
 RAC_API int rac_mesh_create_parts(const float* h_verts, int V, const int32_t* h_faces, int T,
                                   const float* h_uv, const uint8_t* h_vcolor,

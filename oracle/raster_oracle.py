@@ -23,7 +23,7 @@ def lib():
         L.oracle_render_batch.restype = ci
         L.oracle_render_batch.argtypes = [vp, ci, vp, ci, vp, vp, vp, ci, ci, vp, vp, vp, vp, ci, ci, ci, vp, vp, vp, ci]
         L.oracle_render_batch_parts.restype = ci
-        L.oracle_render_batch_parts.argtypes = [vp, ci, vp, ci, vp, vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, vp, vp, vp, ci]
+        L.oracle_render_batch_parts.argtypes = [vp, ci, vp, ci, vp, vp, vp, ci, vp, vp, vp, vp, vp, vp, vp, vp, vp, ci, ci, ci, vp, vp, vp, ci]
         L.oracle_prepare_model_input.restype = ci
         L.oracle_prepare_model_input.argtypes = [vp, vp, vp, ci, ci, ci, ci, vp, ci]
         L.oracle_num_threads.restype = ci
@@ -64,9 +64,10 @@ def render_batch(mesh, T_CO, K, img_size, scene=None, nthreads=0, want_rgba8=Tru
         ptw = np.ascontiguousarray([t.shape[1] if t is not None else 0 for t in texs], dtype=np.int32)
         pth = np.ascontiguousarray([t.shape[0] if t is not None else 0 for t in texs], dtype=np.int32)
         puse = np.ascontiguousarray([int(bool(p.get("use_vcolor", False))) for p in parts], dtype=np.int32)
+        pds = np.ascontiguousarray([int(bool(p.get("double_sided", False))) for p in parts], dtype=np.int32)
         fp = np.ascontiguousarray(mesh.face_part, dtype=np.uint8)
         rc = lib().oracle_render_batch_parts(_p(verts), len(verts), _p(faces), len(faces), _p(uv), _p(vc), _p(fp), n, _p(pmat),
-                                             ctypes.cast(ptex, ctypes.c_void_p), _p(ptw), _p(pth), _p(puse), _p(sc), _p(T), _p(Kc),
+                                             ctypes.cast(ptex, ctypes.c_void_p), _p(ptw), _p(pth), _p(puse), _p(pds), _p(sc), _p(T), _p(Kc),
                                              B, W, H, _p(rgb), _p(depth), _p(rgba8), int(nthreads))
     else:
         rc = lib().oracle_render_batch(_p(verts), len(verts), _p(faces), len(faces), _p(uv), _p(vc), _p(tex), tw, th,

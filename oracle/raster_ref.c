@@ -59,6 +59,7 @@ typedef struct {
     int nparts;
     const float* part_material;   /* nparts*6 */
     const int* part_use_vcolor;   /* nparts */
+    const int* part_double_sided; /* nparts: glTF doubleSided — back faces are drawn (normal not flipped) */
     const int* part_tw;           /* nparts */
     const int* part_th;
     const struct Mips_s* part_mips;
@@ -138,6 +139,7 @@ typedef struct {
     /* oriented so that the interior is on the >= 0 side of every edge */
     int X[3], Y[3];
     float iz0, gx, gy;
+    int mesh_order;   /* 1: vertices kept in mesh order (drawn back face of a doubleSided part), 0: v1 <-> v2 swapped */
 } Setup;
 
 /* returns 1 if the triangle is front-facing, non-degenerate and inside the depth/guard limits */
@@ -146,13 +148,18 @@ static int tri_setup(const OMesh* m, int t, const float* T, const float* K, floa
     for (int k = 0; k < 3; ++k)
         if (!project(T, K, m->verts + 3 * (size_t)m->faces[3 * t + k], znear, &q.X[k], &q.Y[k], &q.iz[k])) return 0;
     int64_t area2 = (int64_t)(q.X[1] - q.X[0]) * (q.Y[2] - q.Y[0]) - (int64_t)(q.X[2] - q.X[0]) * (q.Y[1] - q.Y[0]);
-    if (area2 >= 0) return 0;   /* R4: front = CCW in GL window space = negative area with v down */
+    int back = 0;
+    if (area2 > 0 && m->face_part && m->part_double_sided) back = m->part_double_sided[m->face_part[t]] != 0;
+    if (area2 >= 0 && !back) return 0;   /* R4: front = CCW in GL window space = negative area with v down */
+    if (area2 == 0) return 0;
+    const int a = back ? 1 : 2, b = back ? 2 : 1;      /* interior on the >= 0 side: swap v1 <-> v2 for front faces */
+    s->mesh_order = back;
     s->X[0] = q.X[0]; s->Y[0] = q.Y[0];
-    s->X[1] = q.X[2]; s->Y[1] = q.Y[2];
-    s->X[2] = q.X[1]; s->Y[2] = q.Y[1];
-    float iz1 = q.iz[2], iz2 = q.iz[1];
+    s->X[1] = q.X[a]; s->Y[1] = q.Y[a];
+    s->X[2] = q.X[b]; s->Y[2] = q.Y[b];
+    float iz1 = q.iz[a], iz2 = q.iz[b];
     s->iz0 = q.iz[0];
-    float area = (float)(-area2);
+    float area = (float)(back ? area2 : -area2);
     float d1 = iz1 - s->iz0, d2 = iz2 - s->iz0;
     float ex1 = (float)(s->X[1] - s->X[0]), ey1 = (float)(s->Y[1] - s->Y[0]);
     float ex2 = (float)(s->X[2] - s->X[0]), ey2 = (float)(s->Y[2] - s->Y[0]);
@@ -249,8 +256,8 @@ static void shade(const OMesh* m, const Mips* mp, const OScene* sc, const float*
     if (use_vc || mp->n) {
         float w[3];
         pbary(s, Pcx, Pcy, w);
-        /* Setup order is (v0, v2, v1) of the mesh face */
-        int id[3] = {m->faces[3 * t], m->faces[3 * t + 2], m->faces[3 * t + 1]};
+        /* Setup order is (v0, v2, v1) of the mesh face, (v0, v1, v2) for a drawn back face */
+        int id[3] = {m->faces[3 * t], m->faces[3 * t + (s->mesh_order ? 1 : 2)], m->faces[3 * t + (s->mesh_order ? 2 : 1)]};
         if (use_vc)
             for (int k = 0; k < 3; ++k) {
                 float v = 0.0f;
@@ -417,12 +424,12 @@ EXPORT int oracle_render_batch(const float* verts, int V, const int32_t* faces, 
 EXPORT int oracle_render_batch_parts(const float* verts, int V, const int32_t* faces, int Tn, const float* uv,
                                      const uint8_t* vcolor, const uint8_t* face_part, int nparts, const float* part_material,
                                      const uint8_t* const* part_tex, const int* part_tw, const int* part_th,
-                                     const int* part_use_vcolor, const float* scene, const float* T_CO, const float* K,
+                                     const int* part_use_vcolor, const int* part_double_sided, const float* scene, const float* T_CO, const float* K,
                                      int B, int W, int H, float* rgb, float* depth, uint8_t* rgba8, int nthreads) {
     OMesh m;
     memset(&m, 0, sizeof(m));
     m.verts = verts; m.faces = faces; m.V = V; m.T = Tn; m.uv = uv; m.vcolor = vcolor;
-    m.face_part = face_part; m.nparts = nparts; m.part_material = part_material; m.part_use_vcolor = part_use_vcolor;
+    m.face_part = face_part; m.nparts = nparts; m.part_material = part_material; m.part_use_vcolor = part_use_vcolor; m.part_double_sided = part_double_sided;
     m.part_tw = part_tw; m.part_th = part_th;
     Mips* pm = (Mips*)calloc((size_t)nparts, sizeof(Mips));
     if (!pm) return -1;

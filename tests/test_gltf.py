@@ -104,3 +104,38 @@ def test_oracle_renders_every_part_with_its_own_material(tmp_path):
     red = (cov[:, 0] > cov[:, 1] + 50) & (cov[:, 0] > cov[:, 2] + 50)
     green = (cov[:, 1] > cov[:, 0] + 50) & (cov[:, 1] > cov[:, 2] + 50)
     assert red.sum() > 100 and green.sum() > 100 and (~red & ~green).sum() > 100
+
+
+def test_double_sided_material_draws_back_faces_unlit(tmp_path):
+    """material.doubleSided (Blender's default export): pyrender disables back-face culling for that material and its
+    shader does not flip the normal, so a quad seen from behind is covered (alpha 255, depth present) and shows ambient
+    light only; with doubleSided false it is culled."""
+    from conftest import intrinsics
+    from oracle import raster_oracle as ro
+    import known_answers as KA
+    q = KA.quad(0.3)
+    T = np.eye(4, dtype=np.float32)[None].copy()
+    T[0, :3, :3] = np.diag([1.0, -1.0, -1.0])           # flip the quad: the camera looks at its back
+    T[0, 2, 3] = 2.0
+    K = intrinsics(1, 96, 96)
+    out = {}
+    for ds in (False, True):
+        path = str(tmp_path / ("quad_%d.glb" % ds))
+        # (the loader's Rx(90) is undone by pre-rotating the vertices: (x, y, z) -> (x, z, -y))
+        v = np.stack([q.verts[:, 0], q.verts[:, 2], -q.verts[:, 1]], 1)
+        gltf.save_glb(path, [dict(verts=v, faces=q.faces, material=(0.8, 0.8, 0.8, 1.0, 0.0, 0.5), double_sided=ds)])
+        m = M.load_mesh(path)
+        assert m.parts[0]["double_sided"] is ds
+        np.testing.assert_allclose(m.verts, q.verts, atol=1e-7)
+        _, depth, rgba = ro.render_batch(m, T, K, 96)
+        out[ds] = (depth, rgba)
+    assert (out[False][0] == 0).all() and (out[False][1][..., 3] == 0).all()
+    depth, rgba = out[True]
+    c = rgba[0, 48, 48]
+    assert depth[0, 48, 48] == pytest.approx(2.0, rel=1e-4) and c[3] == 255
+    # ambient only: base * 0.1 (+ n.l clamped to 0.001 of direct light) -> (0.8 * 0.1)^(1/2.2) * 255 = 81
+    assert abs(int(c[0]) - 81) <= 2 and c[0] == c[1] == c[2]
+    # the front of the same quad is lit
+    T[0, :3, :3] = np.eye(3)
+    _, _, front = ro.render_batch(m, T, K, 96)
+    assert front[0, 48, 48, 0] > 150

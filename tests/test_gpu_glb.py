@@ -101,3 +101,26 @@ def test_device_mesh_cache_is_bounded(monkeypatch):
     again = rac.render_batch_device(T, meshes[:B], K, S, want_rgb=False)["depth"]      # long evicted: uploaded again
     assert torch.equal(first, again)
     M.clear_cache()
+
+
+def test_double_sided_open_mesh_matches_oracle(tmp_path):
+    """An OPEN textured surface (a bumpy sphere with 40 % of its faces removed) whose material is doubleSided: through the
+    holes the inside of the far wall is visible — drawn back faces, unlit, with the right texture coordinates (the
+    attribute order of an unswapped record).  Coverage / depth / colour bars against the oracle; and the same file
+    without doubleSided must show fewer covered pixels."""
+    import rac
+    from rac import gltf
+    from rac import mesh as M
+    body = M.with_texture(M.bumpy_sphere(level=4, seed=3, decimate_to=3000), size=64, seed=1)
+    B, W, H = 4, 240, 200
+    T, _ = sample_poses(B, seed=6)
+    K = intrinsics(B, W, H)
+    cov = {}
+    for ds in (True, False):
+        path = str(tmp_path / ("open_%d.glb" % ds))
+        gltf.save_glb(path, [dict(verts=body.verts, faces=body.faces, uv=body.uv, tex=body.tex, material=(1, 1, 1, 1, 0.1, 0.6), double_sided=ds)])
+        m = M.load_mesh(path)
+        out = rac.render_batch_device(T, path, K, (W, H), want_rgba8=True)
+        compare(out, ro.render_batch(m, T, K, (W, H)), W, H, "double_sided=%s" % ds)
+        cov[ds] = (out["depth"] > 0).float().mean().item()
+    assert cov[True] > cov[False] * 1.1, cov
