@@ -4,7 +4,9 @@
 // implements the same spec independently):
 //   RS-V  vertex:  pc = R p + t (fma chain x,y,z order), iz = 1/zc, u = fma(fx, xc*iz, cx),
 //         v = fma(fy, yc*iz, cy); snapped to 1/256 px: X = rint(256 u), Y = rint(256 v).
-//         A triangle with any vertex zc < znear or |u|,|v| > 16384 px is dropped (no clipping).
+//         Near plane: GL clips a triangle at z = znear; here every SAMPLE with d < 0 (z < znear) is rejected by the depth
+//         test (RS-Z), which is the same set of samples, as long as the triangle can be projected at all: a triangle
+//         with any vertex at zc < znear / 64 (0.8 mm for pyrender's 0.05 m) or with |u|,|v| > 16384 px is dropped whole.
 //   RS-T  triangle: area2 = (X1-X0)(Y2-Y0) - (X2-X0)(Y1-Y0) in int64; front-facing iff
 //         area2 < 0 (GL CCW after the v-flip, R4); v1<->v2 are swapped so the interior is E>=0.
 //   RS-C  coverage: 4 samples per pixel at subpixel (96,32),(224,96),(32,160),(160,224)/256,
@@ -24,6 +26,7 @@ namespace rac {
 
 constexpr int kSubpix = 256;          // 8 subpixel bits
 constexpr float kGuardPx = 16384.0f;  // guard band in pixels
+constexpr float kNearRelax = 1.0f / 64.0f;   // vertices are projected down to znear / 64; the near plane clips per sample
 constexpr unsigned kDepthMax = 0xFFFFFFu;
 constexpr unsigned long long kKeyEmpty = ~0ull;
 constexpr int kTileW = 32;            // raster tile in pixels: 32 x 16 (visibility buffer: 512 px * 4 samples * 8 B = 16 KB);

@@ -28,7 +28,7 @@ __device__ __forceinline__ bool project_vertex(const CamPose& c, const float* __
     const float xc = __fmaf_rn(c.r[2], pz, __fmaf_rn(c.r[1], py, __fmaf_rn(c.r[0], px, c.t[0])));
     const float yc = __fmaf_rn(c.r[5], pz, __fmaf_rn(c.r[4], py, __fmaf_rn(c.r[3], px, c.t[1])));
     const float zc = __fmaf_rn(c.r[8], pz, __fmaf_rn(c.r[7], py, __fmaf_rn(c.r[6], px, c.t[2])));
-    if (!(zc >= znear)) return false;
+    if (!(zc >= znear * kNearRelax)) return false;       // (see RS-V: the near plane itself clips per sample, in depth_key)
     iz = __frcp_rn(zc);      // correctly rounded: == 1.0f / zc
     const float u = __fmaf_rn(c.fx, __fmul_rn(xc, iz), c.cx);
     const float v = __fmaf_rn(c.fy, __fmul_rn(yc, iz), c.cy);

@@ -116,7 +116,7 @@ static int project(const float* T, const float* K, const float* p, float znear, 
     float xc = fmaf(T[2], p[2], fmaf(T[1], p[1], fmaf(T[0], p[0], T[3])));
     float yc = fmaf(T[6], p[2], fmaf(T[5], p[1], fmaf(T[4], p[0], T[7])));
     float zc = fmaf(T[10], p[2], fmaf(T[9], p[1], fmaf(T[8], p[0], T[11])));
-    if (!(zc >= znear)) return 0;
+    if (!(zc >= znear * (1.0f / 64.0f))) return 0;   /* RS-V: projectable down to znear / 64; the near plane clips per sample (d < 0) */
     float inv = 1.0f / zc;
     float xn = xc * inv, yn = yc * inv;
     float u = fmaf(K[0], xn, K[2]);

@@ -149,3 +149,27 @@ def check_minified_checker(render, tol=1):
         assert (np.abs(got - want) <= tol).all(), (r, c, got, want)
     inner = rgba8[0, H // 2 - 6:H // 2 + 6, W // 2 - 6:W // 2 + 6, 0].astype(int)
     assert inner.max() - inner.min() <= 3, "a minified 1-texel checker must resolve to a flat grey"
+
+
+def check_near_plane_clips_per_sample(render):
+    """GL clips a triangle at z = znear (0.05 m); the spec rejects every sample with z < znear in the depth test instead,
+    which selects the same samples.  A long floor-like quad running from z = 0.02 m to z = 1.0 m below the optical axis:
+    every covered pixel has depth >= znear, coverage reaches right down to the plane, and the rows that would show the
+    part in front of the plane stay empty."""
+    from rac import mesh as M
+    W, H, fx = 96, 96, 100.0
+    K = np.array([[[fx, 0, W / 2.0], [0, fx, H / 2.0], [0, 0, 1]]], np.float32)
+    y0 = 0.02                                   # 2 cm below the axis (image y grows downwards)
+    v = np.array([[-0.01, y0, 0.02], [0.01, y0, 0.02], [0.3, y0, 1.0], [-0.3, y0, 1.0]], np.float32)
+    f = np.array([[0, 1, 2], [0, 2, 3]], np.int32)      # seen from above (camera at the origin, looking along +z)
+    T = np.eye(4, dtype=np.float32)[None].copy()
+    depth, rgba8 = render(M.Mesh(v, f), T, K, (W, H))
+    cov = depth[0] > 0
+    assert cov.sum() > 50, "the part of the floor beyond the near plane must be visible"
+    assert depth[0][cov].min() >= 0.05 - 1e-6
+    assert depth[0][cov].min() < 0.0515, "coverage must reach down to the near plane (depth %.4f)" % depth[0][cov].min()
+    # a point at depth z projects to row cy + fx * y0 / z: z = znear -> row 88; nothing may be drawn below it
+    row_near = H / 2.0 + fx * y0 / 0.05
+    rows = np.nonzero(cov.any(1))[0]
+    assert rows.max() <= int(row_near) and rows.max() >= int(row_near) - 1
+    assert rows.min() <= H // 2 + 3              # the far end (z = 1 m) sits 2 px below the centre row

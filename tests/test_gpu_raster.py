@@ -188,7 +188,7 @@ def test_edge_cases(rac):
     T[0, 2, 3] = 2.5                      # visible
     T[1, 2, 3] = -2.5                     # behind the camera -> empty
     T[2, 2, 3] = 2.5; T[2, 0, 3] = 50.0   # far off-screen -> empty
-    T[3, 2, 3] = 0.2                      # straddles the near plane: triangles with a vertex < znear are dropped
+    T[3, 2, 3] = 0.2                      # the near face lies exactly ON the near plane (z = 0.05)
     out = rac.render_batch_device(T, m, K, S, want_rgba8=True)
     orc = ro.render_batch(m, T, K, S)
     compare(out, orc, S, S, "edge")
@@ -532,3 +532,8 @@ def test_resolve_is_the_mean_of_four_samples_and_depth_is_sample_zero(rac):
 def test_texture_lod_of_a_minified_checker(rac):
     import known_answers as KA
     KA.check_minified_checker(_gpu_render(rac), tol=2)
+
+
+def test_near_plane_clips_per_sample(rac):
+    import known_answers as KA
+    KA.check_near_plane_clips_per_sample(_gpu_render(rac))

@@ -167,3 +167,8 @@ def test_resolve_is_the_mean_of_four_samples_and_depth_is_sample_zero():
 def test_texture_lod_of_a_minified_checker():
     import known_answers as KA
     KA.check_minified_checker(_oracle_render)
+
+
+def test_near_plane_clips_per_sample():
+    import known_answers as KA
+    KA.check_near_plane_clips_per_sample(_oracle_render)
