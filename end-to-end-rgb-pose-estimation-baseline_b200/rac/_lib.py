@@ -126,16 +126,36 @@ def check(rc, exc=RacError):
     raise exc(f"librac_b200 error {rc}: {msg}")
 
 
+_cuda_ok = False
+
+
 def require_cuda():
+    global _cuda_ok
     import torch
-    if not torch.cuda.is_available():
-        raise RacError("no CUDA device: the render-and-compare path is CUDA-only (sm_100a) and has no CPU fallback")
+    if not _cuda_ok:          # (checked until it succeeds once: a process does not lose its CUDA device)
+        if not torch.cuda.is_available():
+            raise RacError("no CUDA device: the render-and-compare path is CUDA-only (sm_100a) and has no CPU fallback")
+        _cuda_ok = True
     return torch.device("cuda", torch.cuda.current_device())
 
 
-def stream_ptr():
+_raw_stream = None
+
+
+def raw_stream(device_index=None):
+    """cudaStream_t of torch's current stream as an int — torch._C._cuda_getCurrentRawStream where it exists (one C call;
+    torch.cuda.current_stream() builds a Stream object through several Python layers, ~10 us, and every C-ABI call of
+    the hot path needs the handle)."""
+    global _raw_stream
     import torch
-    return c_void_p(torch.cuda.current_stream().cuda_stream)
+    if _raw_stream is None:
+        fast = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+        _raw_stream = fast if fast is not None else (lambda i: torch.cuda.current_stream(i).cuda_stream)
+    return _raw_stream(torch.cuda.current_device() if device_index is None else device_index)
+
+
+def stream_ptr():
+    return c_void_p(raw_stream())
 
 
 def ptr(t):

@@ -18,7 +18,7 @@ _ws_cache = {}
 def _workspace(dev, nbytes):
     """Grow-only scratch per (device, stream), at most 8 of them.  Reuse is stream-ordered: every kernel of a call is enqueued on
     the current stream, so a later call on the same stream cannot overtake an earlier one."""
-    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    key = (dev.index, _lib.raw_stream(dev.index))
     ws = _ws_cache.get(key)
     if ws is None or ws.numel() < nbytes:
         if ws is None:
