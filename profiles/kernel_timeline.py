@@ -8,7 +8,7 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "end-to-end-rgb-pose-estimation-baseline_b200")
-OUT = os.path.join(PKG, "librac_b200_timing.so")
+OUT = os.environ.get("RAC_TIMING_LIB", os.path.join(PKG, "librac_b200_timing.so"))
 sys.path[:0] = [PKG, ROOT]
 NAMES = ["gt_norm (side)", "setup", "raster", "finalize_live"]
 
