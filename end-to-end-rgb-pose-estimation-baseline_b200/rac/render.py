@@ -254,10 +254,12 @@ def _gt_cache_key(t, dev):
     return None
 
 
-def _gt_cache_lookup(t, dev):
+def _gt_cache_lookup(t, dev, kv=None):
+    """kv: a (key, validator) pair already computed by _gt_cache_key for this very call (the fingerprint of a host array
+    costs ~0.1 ms: take it once per prepare_model_input, not once per lookup and once per store)."""
     if not _gt_cache_enabled:
         return None
-    kv = _gt_cache_key(t, dev)
+    kv = kv or _gt_cache_key(t, dev)
     if kv is None:
         return None
     for e in _gt_cache:
@@ -266,10 +268,10 @@ def _gt_cache_lookup(t, dev):
     return None
 
 
-def _gt_cache_store(t, dev, planes):
+def _gt_cache_store(t, dev, planes, kv=None):
     if not _gt_cache_enabled:
         return
-    kv = _gt_cache_key(t, dev)
+    kv = kv or _gt_cache_key(t, dev)
     if kv is None:
         return
     import weakref
@@ -448,7 +450,8 @@ def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
         assert d.shape == (B, H, W)
     C = 7 if use_norm_depth else 6
     x = torch.empty((B, C, H, W), dtype=torch.float32, device=dev)
-    cached = _gt_cache_lookup(gt_hwc, dev)
+    kv = _gt_cache_key(gt_hwc, dev) if _gt_cache_enabled else None      # (taken BEFORE anything is uploaded: it must describe
+    cached = _gt_cache_lookup(gt_hwc, dev, kv)                          # the content the planes are computed from)
     if cached is not None:
         x[:, C - 3:].copy_(cached)
         _assemble_call(L, init, None, d, B, W, H, use_norm_depth, x, dev)
@@ -457,7 +460,7 @@ def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
     if _is_u8(gt_hwc):
         gt_norm_u8_device(gt_hwc, x, use_norm_depth)
         _assemble_call(L, init, None, d, B, W, H, use_norm_depth, x, dev)
-        _gt_cache_store(gt_hwc, dev, x[:, C - 3:])
+        _gt_cache_store(gt_hwc, dev, x[:, C - 3:], kv)
         return x
     host = _host_view(gt_hwc) if not capturing else None
     if host is not None and host.dtype == np.float64:
@@ -466,15 +469,15 @@ def assemble_input_device(init_hwc, gt_hwc, depth, use_norm_depth=False):
             buf, ring, slot = packed
             gt_norm_u8_device(buf, x, use_norm_depth, _host_slot=(ring, slot))
             _assemble_call(L, init, None, d, B, W, H, use_norm_depth, x, dev)
-            _gt_cache_store(gt_hwc, dev, x[:, C - 3:])
+            _gt_cache_store(gt_hwc, dev, x[:, C - 3:], kv)
             return x
     if host is not None and host.dtype in (np.float32, np.float64) and B >= 2 * _GT_CHUNKS:
         _upload_f32_chunked(L, gt_hwc, init, d, B, W, H, use_norm_depth, x, dev, host_convert=not _overlappable(gt_hwc))
-        _gt_cache_store(gt_hwc, dev, x[:, C - 3:])
+        _gt_cache_store(gt_hwc, dev, x[:, C - 3:], kv)
         return x
     gt = torch.as_tensor(gt_hwc).to(device=dev, dtype=torch.float32).contiguous()
     _assemble_call(L, init, gt, d, B, W, H, use_norm_depth, x, dev)
-    _gt_cache_store(gt_hwc, dev, x[:, C - 3:])
+    _gt_cache_store(gt_hwc, dev, x[:, C - 3:], kv)
     return x
 
 
