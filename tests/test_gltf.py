@@ -139,3 +139,51 @@ def test_double_sided_material_draws_back_faces_unlit(tmp_path):
     T[0, :3, :3] = np.eye(3)
     _, _, front = ro.render_batch(m, T, K, 96)
     assert front[0, 48, 48, 0] > 150
+
+
+def _write_glb(path, g, blob):
+    js = json.dumps(g).encode()
+    js += b" " * (-len(js) % 4)
+    blob += b"\0" * (-len(blob) % 4)
+    with open(path, "wb") as f:
+        f.write(struct.pack("<4sII", b"glTF", 2, 12 + 8 + len(js) + 8 + len(blob)))
+        f.write(struct.pack("<I4s", len(js), b"JSON") + js + struct.pack("<I4s", len(blob), b"BIN\0") + blob)
+
+
+def test_accessor_variants(tmp_path):
+    """Un-indexed primitive (POSITION order = triangle list), float VEC3 COLOR_0 on a material-less primitive, normalised
+    uint16 TEXCOORD_0, uint8 indices, an accessor without a bufferView (zeros), and a file with no triangle primitive."""
+    pos = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [1, 0, 0], [1, 1, 0], [0, 1, 0]], "<f4")
+    col = np.array([[1.0, 0.5, 0.0]] * 6, "<f4")
+    uv16 = np.array([[0, 0], [65535, 0], [0, 65535], [65535, 0], [65535, 65535], [0, 65535]], "<u2")
+    idx8 = np.array([0, 1, 2, 3, 4, 5], "u1")
+    parts = [pos.tobytes(), col.tobytes(), uv16.tobytes(), idx8.tobytes()]
+    offs = np.cumsum([0] + [len(p) + (-len(p) % 4) for p in parts])
+    blob = b"".join(p + b"\0" * (-len(p) % 4) for p in parts)
+    views = [{"buffer": 0, "byteOffset": int(offs[i]), "byteLength": len(parts[i])} for i in range(4)]
+    g = {"asset": {"version": "2.0"}, "buffers": [{"byteLength": len(blob)}], "bufferViews": views,
+         "accessors": [{"bufferView": 0, "componentType": 5126, "count": 6, "type": "VEC3"},
+                       {"bufferView": 1, "componentType": 5126, "count": 6, "type": "VEC3"},
+                       {"bufferView": 2, "componentType": 5123, "count": 6, "type": "VEC2", "normalized": True},
+                       {"bufferView": 3, "componentType": 5121, "count": 6, "type": "SCALAR"},
+                       {"componentType": 5126, "count": 6, "type": "VEC2"}],
+         "materials": [{"pbrMetallicRoughness": {"baseColorFactor": [0.5, 0.25, 1.0, 1.0]}, "doubleSided": True}],
+         "meshes": [{"primitives": [{"attributes": {"POSITION": 0, "COLOR_0": 1}},                          # no indices, no material
+                                    {"attributes": {"POSITION": 0, "TEXCOORD_0": 2}, "indices": 3, "material": 0},
+                                    {"attributes": {"POSITION": 0, "TEXCOORD_0": 4}, "material": 0}]}]}
+    path = str(tmp_path / "variants.glb")
+    _write_glb(path, g, blob)
+    m = gltf.load_glb(path, apply_rx90=False)
+    assert len(m.parts) == 3 and len(m.faces) == 6 and len(m.verts) == 18
+    np.testing.assert_array_equal(m.faces[:2], [[0, 1, 2], [3, 4, 5]])
+    assert m.parts[0]["use_vcolor"] and (m.vcolor[:6] == [255, 128, 0, 255]).all()          # float VEC3 colours, alpha 255
+    np.testing.assert_allclose(m.uv[6:12], uv16 / 65535.0, atol=1e-7)                       # normalised u16 texcoords
+    np.testing.assert_array_equal(m.faces[2:4] - 6, [[0, 1, 2], [3, 4, 5]])                 # u8 indices
+    assert (m.uv[12:18] == 0).all()                                                         # accessor without a bufferView
+    np.testing.assert_allclose(m.parts[1]["material"], (128 / 255, 64 / 255, 1.0, 1.0, 1.0, 1.0))
+    assert m.parts[1]["double_sided"] and not m.parts[0]["double_sided"]
+    g2 = dict(g, meshes=[{"primitives": [{"attributes": {"POSITION": 0}, "mode": 0}]}])
+    p2 = str(tmp_path / "points.glb")
+    _write_glb(p2, g2, blob)
+    with pytest.raises(ValueError):
+        gltf.load_glb(p2)
