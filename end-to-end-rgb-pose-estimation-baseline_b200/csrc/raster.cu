@@ -313,6 +313,37 @@ __global__ void rac_debug_epoch_kernel() {
 }
 #endif
 
+// ---------------------------------------------------------------------------------------------
+// rac_assemble_input_static: scratch that nobody has to allocate
+// ---------------------------------------------------------------------------------------------
+// The per-image depth statistics that rac_assemble_input keeps in caller-provided scratch (one 64-byte ImgStats per
+// image) live here in a fixed array that is part of the library's device image.  Each GPU that loads librac_b200 owns
+// one copy (RAC_ASSEMBLE_STATIC_MAX_B * 64 B = 64 KiB) from module load until the process exits.
+//
+// In HOST code the identifier `g_assemble_static` is only a handle for the runtime's symbol table; it is not a device
+// address and must never be handed to a kernel.  The address that is valid on the GPU comes from
+// cudaGetSymbolAddress, asked once per device while that device is current, and is remembered per device ordinal.
+static __device__ __align__(256) unsigned char g_assemble_static[RAC_ASSEMBLE_STATIC_MAX_B * sizeof(rac::ImgStats)];
+
+constexpr int kStaticMaxDevices = 64;
+static std::atomic<void*> g_assemble_static_addr[kStaticMaxDevices];
+
+// Device address of g_assemble_static on the CURRENT device.  The first call on a device performs the symbol lookup
+// (which may load the module and synchronise — hence "not inside a stream capture"); later calls are one atomic load.
+static int assemble_static_scratch(void** out) {
+    int dev = 0;
+    RAC_CUDA_CHECK(cudaGetDevice(&dev));
+    RAC_REQUIRE(dev >= 0 && dev < kStaticMaxDevices, "rac_assemble_input_static: device ordinal %d out of range", dev);
+    void* p = g_assemble_static_addr[dev].load(std::memory_order_acquire);
+    if (!p) {
+        RAC_CUDA_CHECK(cudaGetSymbolAddress(&p, g_assemble_static));
+        RAC_REQUIRE(p != nullptr, "rac_assemble_input_static: cudaGetSymbolAddress returned a null address");
+        g_assemble_static_addr[dev].store(p, std::memory_order_release);   // (two racing threads store the same value)
+    }
+    *out = p;
+    return RAC_OK;
+}
+
 extern "C" {
 
 #ifdef RAC_PHASE_TIMING
@@ -393,6 +424,23 @@ int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, const flo
     assemble_render_kernel<<<dim3((npix + kFinChunkPix - 1) / kFinChunkPix, B), 256, 0, stream>>>(fin);
     RAC_LAUNCHED();
     return RAC_OK;
+}
+
+// rac_assemble_input for callers that cannot allocate device memory (see include/rac.h).  Same kernels, same
+// arithmetic; the only difference is where the ImgStats scratch lives.  Nothing in here allocates: no cudaMalloc /
+// cudaFree, no stream or event creation, no torch.  rac_assemble_input clears the B records it is about to use with a
+// cudaMemsetAsync on `stream`, which is what makes the array reusable although it still holds the previous call's sums.
+int rac_assemble_input_static(const float* d_init_hwc, const float* d_gt_hwc, const float* d_depth, int B, int W, int H,
+                              int use_norm_depth, float* d_x_nchw, rac_stream_t stream_) {
+    RAC_REQUIRE(B > 0, "rac_assemble_input_static: bad batch size B=%d", B);
+    RAC_REQUIRE(B <= RAC_ASSEMBLE_STATIC_MAX_B,
+                "rac_assemble_input_static: B=%d exceeds the built-in scratch (RAC_ASSEMBLE_STATIC_MAX_B = %d images); "
+                "split the batch or use rac_assemble_input with scratch of your own", B, RAC_ASSEMBLE_STATIC_MAX_B);
+    void* scratch = nullptr;
+    const int rc = assemble_static_scratch(&scratch);
+    if (rc != RAC_OK) return rc;
+    return rac_assemble_input(d_init_hwc, d_gt_hwc, d_depth, B, W, H, use_norm_depth, d_x_nchw, scratch,
+                              sizeof(g_assemble_static), stream_);
 }
 
 }  // extern "C"

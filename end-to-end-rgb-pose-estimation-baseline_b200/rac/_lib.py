@@ -52,6 +52,7 @@ SIGNATURES = {
     "rac_assemble_workspace_bytes": (c_size_t, [c_int]),
     "rac_assemble_input": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
                                    c_size_t, c_void_p]),
+    "rac_assemble_input_static": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "rac_pose_update_fwd": (c_int, [c_void_p, c_int, c_void_p, c_int, c_double, c_double, c_int, c_void_p, c_void_p,
                                     c_void_p]),
     "rac_pose_update_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]),

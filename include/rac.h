@@ -153,6 +153,25 @@ RAC_API int rac_assemble_input(const float* d_init_hwc, const float* d_gt_hwc, c
                                int B, int W, int H, int use_norm_depth, float* d_x_nchw,
                                void* d_stats_ws, size_t ws_bytes, rac_stream_t stream);
 
+/* No counterpart in the reference: this exists for hosts of the library, not for a reference function.
+ * It is rac_assemble_input (above) without the d_stats_ws argument, for callers that are not in a position to
+ * allocate device memory: code running where a cudaMalloc would be refused or would stall — inside a real-time or
+ * serving loop that forbids allocation after start-up, under a framework that owns the whole GPU heap through its own
+ * pool and hands out no raw allocations to plug-ins, or in a process whose memory budget is fixed and audited up front.
+ * The per-image statistics scratch is a fixed array inside the library's device image instead
+ * (RAC_ASSEMBLE_STATIC_MAX_B records of 64 B = 64 KiB per GPU that loads the library, held until the process exits).
+ * The call itself allocates nothing on host or device; inputs and outputs are still the caller's.
+ *  - B > RAC_ASSEMBLE_STATIC_MAX_B returns RAC_E_INVALID with a message that names the limit; split the batch.
+ *  - The first call on each device looks up the array's device address (a one-time set-up that may load the module
+ *    and synchronise).  Make that first call during start-up, before any stream capture begins on that device.
+ *  - All calls on one GPU share the one array and it keeps whatever the last call left in it; every call begins by
+ *    clearing the B records it uses, in stream order.  Two calls whose GPU work can overlap (different streams
+ *    without an ordering between them, or two host threads) race on it and produce wrong depth planes — order them.
+ * Results are identical to rac_assemble_input's on the same inputs. */
+#define RAC_ASSEMBLE_STATIC_MAX_B 1024
+RAC_API int rac_assemble_input_static(const float* d_init_hwc, const float* d_gt_hwc, const float* d_depth,
+                                      int B, int W, int H, int use_norm_depth, float* d_x_nchw, rac_stream_t stream);
+
 /* ---- step 3+4: rotation head + SE(3) update ------------------------------
  * ref: rotation_representation.py:131-184 (calculate_T_CO_pred) over
  *      :4-19 (6D), :22-39 (SVD), :41-118 (exp map).
