@@ -201,25 +201,34 @@ def _assemble_call(L, init, gt, d, B, W, H, use_norm_depth, x, dev):
 # The reference normalises and re-uploads the SAME gt crop in every refinement iteration of a batch
 # (train_model.py:234-250: `gt_imgs` is drawn once, prepare_model_input runs inside the `for j` loop).  The normalised
 # planes of the last few crops stay on the device and later iterations skip the upload and the normalisation
-# (SURVEY.md §8f N1).  What identifies "the same crop":
-#   host arrays (numpy — what the drivers pass, train_model.py:226 — and CPU tensors): address, shape, dtype, strides
-#       AND a content fingerprint taken at insert and at lookup — the raw bytes of ~2 k values strided across the whole
-#       array (32 per image at batch 64; every sample is a cache miss in pageable memory, ~80 ns each) plus its first and last 256 values.  A buffer refilled with another batch
-#       (through a numpy view, from_numpy-shared storage, in place, ...) differs in the fingerprint and misses; torch's
-#       version counter is NOT consulted (it does not see writes through numpy views);
+# (SURVEY.md §8f N1).  The reference itself recomputes on every call (data_loaders.py:163-166), so a hit must mean
+# "the same object, holding what it held when the planes were made".  What counts as that:
+#   host arrays (numpy — what the drivers pass, train_model.py:226 — and CPU tensors):
+#     (1) IDENTITY: a weak reference to the very object that was passed.  A new array never hits, whatever address the
+#         allocator gave it (the unchanged driver allocates a new `gt_imgs` per batch and freed addresses come back);
+#     (2) CONTENT, against in-place refills of that object (through a numpy view, from_numpy-shared storage, ...; torch's
+#         version counter does not see those): a fingerprint taken at insert and at every lookup — the raw bytes of one
+#         pixel (all three channels) out of every _FP_LATTICE x _FP_LATTICE block of EVERY image, on a lattice whose
+#         column offset shifts from row band to row band (no aliasing with the row pitch), plus the first and last 256
+#         values.  ~0.4 ms at 64 x 320 x 240 (19 200 cache lines of pageable memory).
+#     Guarantee: an in-place edit that changes every pixel of some 16 x 16 block of some image (a refilled buffer, a
+#     replaced image, a pasted / augmented region of that size) is always a miss.  NOT guaranteed: edits smaller than
+#     the lattice (single pixels, thin lines) between two calls on the same object — a caller that edits crops in place
+#     at that granularity between refinement iterations switches the cache off: rac.render.set_gt_cache(False).
 #   CUDA tensors: object identity, storage pointer and in-place version counter (no host copy of a fingerprint
 #       without a sync; device buffers cannot be written behind torch's back through numpy).
-# A miss costs one upload, never a stale image.
-_gt_cache = []          # [dict(key, fp | ref+version, dev, planes (B,3,H,W))], most recent last
+_gt_cache = []          # [dict(key, val, ref, planes (B,3,H,W))], most recent last
 _GT_CACHE_ENTRIES = 2
 _gt_cache_enabled = True
-_FP_STRIDED = 2048
+_FP_LATTICE = 16
 _FP_EDGE = 256
+_fp_index = {}          # (B, H, W) -> flat pixel indices of the lattice (int64)
 
 
 def set_gt_cache(enabled):
-    """Switch the cross-iteration gt cache on/off (bench.py's fresh-crop-every-step figure switches it off: every
-    step must pay its own upload); returns the previous setting."""
+    """Switch the cross-iteration gt cache on/off; returns the previous setting.  Off = every prepare_model_input
+    uploads and normalises its crop, exactly like the reference (use it when crops are edited in place at a finer
+    granularity than the fingerprint lattice; bench.py's fresh-crop-every-step figure also switches it off)."""
     global _gt_cache_enabled
     prev = _gt_cache_enabled
     _gt_cache_enabled = bool(enabled)
@@ -237,17 +246,35 @@ def _host_view(t):
     return None
 
 
+def _lattice(B, H, W):
+    idx = _fp_index.get((B, H, W))
+    if idx is None:
+        s = _FP_LATTICE
+        per = []
+        for j, y in enumerate(range(min(s // 2, H - 1), H, s)):
+            xs = np.arange((5 * j) % s, W, s, dtype=np.int64)      # 5 is coprime to 16: the offset walks all residues
+            per.append(y * W + xs)
+        per = np.concatenate(per)
+        idx = (np.arange(B, dtype=np.int64)[:, None] * (H * W) + per[None]).reshape(-1)
+        if len(_fp_index) >= 8:
+            _fp_index.clear()
+        _fp_index[(B, H, W)] = idx
+    return idx
+
+
 def _fingerprint(a):
+    """a: C-contiguous (B,H,W,3) host array."""
+    B, H, W, C = a.shape
     flat = a.reshape(-1)
-    n = flat.size
-    step = max(1, n // _FP_STRIDED)
-    return flat[::step].tobytes() + flat[:_FP_EDGE].tobytes() + flat[-_FP_EDGE:].tobytes()
+    return np.take(a.reshape(B * H * W, C), _lattice(B, H, W), axis=0).tobytes() + flat[:_FP_EDGE].tobytes() + flat[-_FP_EDGE:].tobytes()
 
 
 def _gt_cache_key(t, dev):
     """-> (key, validator) or None when `t` cannot be cached."""
     a = _host_view(t)
     if a is not None:
+        if a.ndim != 4 or a.size == 0:
+            return None
         return ("host", a.__array_interface__["data"][0], a.shape, a.dtype.str, a.strides, dev.index), _fingerprint(a)
     if isinstance(t, torch.Tensor) and t.is_cuda:
         return ("cuda", id(t), t.data_ptr(), tuple(t.shape), str(t.dtype), dev.index), t._version
@@ -256,14 +283,14 @@ def _gt_cache_key(t, dev):
 
 def _gt_cache_lookup(t, dev, kv=None):
     """kv: a (key, validator) pair already computed by _gt_cache_key for this very call (the fingerprint of a host array
-    costs ~0.1 ms: take it once per prepare_model_input, not once per lookup and once per store)."""
+    costs a few tenths of a millisecond: take it once per prepare_model_input, not once per lookup and once per store)."""
     if not _gt_cache_enabled:
         return None
     kv = kv or _gt_cache_key(t, dev)
     if kv is None:
         return None
     for e in _gt_cache:
-        if e["key"] == kv[0] and e["val"] == kv[1] and (e["ref"] is None or e["ref"]() is t):
+        if e["ref"]() is t and e["key"] == kv[0] and e["val"] == kv[1]:
             return e["planes"]
     return None
 
@@ -275,8 +302,11 @@ def _gt_cache_store(t, dev, planes, kv=None):
     if kv is None:
         return
     import weakref
-    ref = weakref.ref(t) if kv[0][0] == "cuda" else None      # id() is only meaningful while the tensor is alive
-    keep = [e for e in _gt_cache if e["key"] != kv[0] and (e["ref"] is None or e["ref"]() is not None)]
+    try:
+        ref = weakref.ref(t)        # identity: an entry whose object has died can never hit (addresses and id()s are recycled)
+    except TypeError:
+        return
+    keep = [e for e in _gt_cache if e["ref"]() is not None and e["ref"]() is not t]
     _gt_cache[:] = keep[-(_GT_CACHE_ENTRIES - 1):] if _GT_CACHE_ENTRIES > 1 else []
     _gt_cache.append({"key": kv[0], "val": kv[1], "ref": ref, "planes": planes.clone()})
 

@@ -301,7 +301,7 @@ def test_assemble_input_pinned_gt_overlapped_upload(rac, B, use_depth):
 def test_gt_cache_across_refinement_iterations(rac):
     """The same gt crop passed again (the reference's `for j` loop, train_model.py:234-250) reuses the normalised planes
     left on the device.  Host arrays — numpy, as the drivers pass them (train_model.py:226), and CPU tensors — are
-    recognised by address + a content fingerprint, so a buffer REFILLED behind torch's back (through a numpy view: no
+    recognised by object identity + a content fingerprint, so a buffer REFILLED behind torch's back (through a numpy view: no
     version bump) misses instead of handing back the previous batch's planes."""
     from rac import render as R
     rng = np.random.default_rng(21)
@@ -331,7 +331,7 @@ def test_gt_cache_across_refinement_iterations(rac):
             np.testing.assert_allclose(x3.cpu().numpy(), assemble_ref.prepare_model_input(init2.cpu().numpy(), as64(gt), None, False).numpy(),
                                        rtol=1e-5, atol=2e-5)
             assert not torch.equal(x3[:, 3:], x2[:, 3:])
-            # one image of the batch replaced: the strided fingerprint covers every image
+            # one image of the batch replaced: the lattice fingerprint covers every image
             view[B - 1] = (rng.integers(0, 256, (H, W, 3)) / 255.0).astype(view.dtype)
             assert R._gt_cache_lookup(gt, x1.device) is None, form
         # CUDA tensors: identity + version counter
@@ -380,6 +380,59 @@ def test_unchanged_loader_crop_travels_as_bytes(rac, use_depth):
         x = rac.assemble_input_device(init, g, depth, use_depth).cpu().numpy()
         np.testing.assert_allclose(x, assemble_ref.prepare_model_input(init.cpu().numpy(), g, depth.cpu().numpy(), use_depth).numpy(),
                                    rtol=1e-5, atol=2e-5)
+    finally:
+        R.set_gt_cache(prev)
+
+
+def test_gt_cache_misses_on_new_objects_and_block_edits(rac):
+    """The cache contract (rac/render.py): a hit needs the SAME live object with an unchanged lattice fingerprint.
+    (a) Object-centred crops on a uniform black background that differ only in the centre, a new numpy array per batch
+        as the unchanged driver allocates them (train_model.py:226) — possibly at the address the freed one had, at a
+        shape (B*H = 2048) where a fixed-stride sample would only ever see pixel column 0: every batch must miss.
+    (b) One 16 x 16 block of one image edited in place between two calls on the same array: must miss.
+    The reference recomputes on every call (data_loaders.py:163-166); every output is checked against that."""
+    from rac import render as R
+    rng = np.random.default_rng(33)
+    B, H, W = 8, 256, 256
+    init = torch.tensor(rng.uniform(0, 1, (B, H, W, 3)).astype(np.float32), device="cuda")
+
+    def centred():
+        g = np.zeros((B, H, W, 3))
+        g[:, 96:160, 96:160] = rng.integers(1, 256, (B, 64, 64, 3)) / 255.0
+        return g
+
+    def expect(g):
+        return assemble_ref.prepare_model_input(init.cpu().numpy(), g, None, False).numpy()
+
+    prev = R.set_gt_cache(True)
+    try:
+        R.set_gt_cache(False); R.set_gt_cache(True)
+        addrs = set()
+        for batch in range(4):
+            g = centred()
+            addrs.add(g.ctypes.data)
+            assert R._gt_cache_lookup(g, init.device) is None, batch
+            x = rac.assemble_input_device(init, g, None, False)
+            np.testing.assert_allclose(x.cpu().numpy(), expect(g), rtol=1e-5, atol=2e-5)
+            assert R._gt_cache_lookup(g, init.device) is not None          # the refinement iterations of THIS batch hit
+            x2 = rac.assemble_input_device(init, g, None, False)
+            assert torch.equal(x, x2)
+            del g
+        # an equal-valued COPY is another object: miss (costs an upload, never a wrong image)
+        g = centred()
+        rac.assemble_input_device(init, g, None, False)
+        assert R._gt_cache_lookup(g.copy(), init.device) is None
+        # (b) in-place block edits at arbitrary (unaligned) positions, in the image centre and in a corner
+        for (b, y0, x0) in [(3, 101, 77), (B - 1, H - 16, W - 16), (0, 0, 0), (5, 13, 200)]:
+            assert R._gt_cache_lookup(g, init.device) is not None
+            g[b, y0:y0 + 16, x0:x0 + 16] = 1.0 - g[b, y0:y0 + 16, x0:x0 + 16]
+            assert R._gt_cache_lookup(g, init.device) is None, (b, y0, x0)
+            x = rac.assemble_input_device(init, g, None, False)
+            np.testing.assert_allclose(x.cpu().numpy(), expect(g), rtol=1e-5, atol=2e-5)
+        # switched off: nothing is kept, every call recomputes
+        R.set_gt_cache(False)
+        rac.assemble_input_device(init, g, None, False)
+        assert R._gt_cache == []
     finally:
         R.set_gt_cache(prev)
 
