@@ -32,6 +32,8 @@ import numpy as np
 _COMP = {5120: ("i1", 1), 5121: ("u1", 1), 5122: ("i2", 2), 5123: ("u2", 2), 5125: ("u4", 4), 5126: ("f4", 4)}
 _NCOMP = {"SCALAR": 1, "VEC2": 2, "VEC3": 3, "VEC4": 4, "MAT2": 4, "MAT3": 9, "MAT4": 16}
 DEFAULT_MATERIAL = (0.3, 0.3, 0.3, 1.0, 0.2, 0.8)          # pyrender's default for primitives without a material
+VERTEX_COLOR_MATERIAL = (1.0, 1.0, 1.0, 1.0, 0.2, 0.8)     # ... and without a material but WITH COLOR_0: white base, the vertex
+                                                            # colour is the base colour (pyrender _get_trimesh_props, kind 'vertex')
 
 
 def _chunks(data):
@@ -126,7 +128,9 @@ def load_glb(path, apply_rx90=True):
                     mat_cache[prim["material"]] = _material(gltf, binary, prim["material"])
                 part = dict(mat_cache[prim["material"]], use_vcolor=False)
             else:
-                part = {"material": DEFAULT_MATERIAL, "tex": None, "use_vcolor": "COLOR_0" in attr, "double_sided": False}
+                has_vc = "COLOR_0" in attr
+                part = {"material": VERTEX_COLOR_MATERIAL if has_vc else DEFAULT_MATERIAL, "tex": None, "use_vcolor": has_vc,
+                        "double_sided": False}
             uv = np.zeros((len(pos), 2), dtype=np.float32)
             if has_mat and "TEXCOORD_0" in attr:
                 uv = _accessor(gltf, binary, attr["TEXCOORD_0"]).astype(np.float32)[:, :2]

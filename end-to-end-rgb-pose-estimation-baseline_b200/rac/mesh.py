@@ -21,6 +21,9 @@ _PLY_TYPES = {
 }
 
 
+VERTEX_COLOR_MATERIAL = (1.0, 1.0, 1.0, 1.0, 0.2, 0.8)     # pyrender: material of a vertex-/face-coloured trimesh without a material
+
+
 class Mesh:
     """Indexed triangle mesh on the host.  verts (V,3) f32, faces (T,3) i32, optional
     uv (V,2) f32, vcolor (V,4) u8, tex (th,tw,3) u8 with row 0 at v = 0 (GL convention)."""
@@ -43,7 +46,13 @@ class Mesh:
         return self.verts
 
     def material_array(self):
+        """(base_color[4], metallic, roughness) of a single-part mesh.  Without an explicit material the choice follows
+        pyrender's Mesh.from_trimesh -> _get_trimesh_props (renderer.py:41): a mesh that carries vertex colours
+        (trimesh visual kind 'vertex', e.g. a coloured PLY) gets baseColorFactor (1, 1, 1, 1) — the vertex colour IS the
+        base colour — and only a mesh with no colours at all gets the 0.3 grey.  Both use metallic 0.2, roughness 0.8."""
         if self.material is None:
+            if self.vcolor is not None and self.tex is None:
+                return np.array(VERTEX_COLOR_MATERIAL, dtype=np.float32)
             return np.array([0.3, 0.3, 0.3, 1.0, 0.2, 0.8], dtype=np.float32)
         return np.asarray(self.material, dtype=np.float32).reshape(6)
 

@@ -87,7 +87,8 @@ RAC_API void rac_material_defaults(rac_material_t* out);
  * Uploads an indexed triangle mesh once; precomputes unit face normals
  * normalize((v1-v0)x(v2-v0)) (flat shading).  h_uv (V,2),
  * h_tex (th,tw,3) RGB8 sRGB, h_vcolor (V,4) RGBA8 are optional (NULL).
- * mat NULL = pyrender default material. */
+ * mat NULL = pyrender default material (0.3 grey).  pyrender gives a vertex-coloured mesh without a material a WHITE
+ * base colour (1,1,1,1; metallic 0.2, roughness 0.8) instead: the Python layer passes that explicitly (rac/mesh.py). */
 RAC_API int rac_mesh_create(const float* h_verts, int V, const int32_t* h_faces, int T,
                             const float* h_uv, const uint8_t* h_tex, int tw, int th,
                             const uint8_t* h_vcolor, const rac_material_t* mat,

@@ -39,10 +39,10 @@ def test_roundtrip_matches_the_reference_semantics(tmp_path):
     np.testing.assert_allclose(m.parts[1]["material"], (204 / 255, 51 / 255, 26 / 255, 1, 0.5, 0.4), atol=1e-7)
     np.testing.assert_array_equal(m.parts[0]["tex"], prims[0]["tex"])
     np.testing.assert_allclose(m.uv[nv[0]:nv[1]], prims[0]["uv"], atol=1e-7)
-    # COLOR_0: ignored on a primitive WITH a material, used (with pyrender's default material) on one WITHOUT
+    # COLOR_0: ignored on a primitive WITH a material, used (on pyrender's white vertex-colour material) on one WITHOUT
     assert not m.parts[1]["use_vcolor"] and (m.vcolor[nv[1]:nv[2]] == 255).all()
     assert m.parts[2]["use_vcolor"] and (m.vcolor[nv[2]:nv[3]] == [10, 200, 30, 255]).all()
-    np.testing.assert_allclose(m.parts[2]["material"], (0.3, 0.3, 0.3, 1.0, 0.2, 0.8))
+    np.testing.assert_allclose(m.parts[2]["material"], (1.0, 1.0, 1.0, 1.0, 0.2, 0.8))
     assert m.parts[1]["tex"] is None and m.parts[2]["tex"] is None
     # the trimesh-compatible vertex source of data_loaders.get_vertices
     assert m.vertices is m.verts
@@ -104,6 +104,43 @@ def test_oracle_renders_every_part_with_its_own_material(tmp_path):
     red = (cov[:, 0] > cov[:, 1] + 50) & (cov[:, 0] > cov[:, 2] + 50)
     green = (cov[:, 1] > cov[:, 0] + 50) & (cov[:, 1] > cov[:, 2] + 50)
     assert red.sum() > 100 and green.sum() > 100 and (~red & ~green).sum() > 100
+
+
+def test_vertex_coloured_mesh_without_material_gets_white_base(tmp_path):
+    """pyrender's material selection (Mesh.from_trimesh -> _get_trimesh_props, reached from renderer.py:41): a trimesh
+    whose visual kind is 'vertex' and that has no material is drawn with baseColorFactor (1,1,1,1), metallic 0.2,
+    roughness 0.8 — the 0.3 grey is for meshes with no colours at all.  Known answer: a mesh with a UNIFORM vertex
+    colour c must render exactly like the uncoloured mesh with base colour c / 255, for coloured PLY files and for
+    material-less COLOR_0 primitives of a .glb alike."""
+    from conftest import intrinsics
+    from oracle import raster_oracle as ro
+    s = M.icosphere(2)
+    c = np.array([200, 120, 40, 255], np.uint8)
+    T = np.eye(4, dtype=np.float32)[None].copy()
+    T[0, :3, 3] = [0.05, -0.02, 2.5]
+    K = intrinsics(1, 96, 96)
+    plain = M.Mesh(s.verts, s.faces, material=(200 / 255, 120 / 255, 40 / 255, 1.0, 0.2, 0.8))
+    _, d_ref, q_ref = ro.render_batch(plain, T, K, 96)
+    assert (d_ref > 0).mean() > 0.1
+    # PLY with per-vertex colours, loaded back from disk
+    ply = str(tmp_path / "c.ply")
+    M.save_ply(ply, M.Mesh(s.verts, s.faces, vcolor=np.tile(c, (len(s.verts), 1))))
+    m = M.load_mesh(ply)
+    assert m.material is None and list(m.material_array()) == pytest.approx([1, 1, 1, 1, 0.2, 0.8])
+    assert list(M.Mesh(s.verts, s.faces).material_array()) == pytest.approx([0.3, 0.3, 0.3, 1, 0.2, 0.8])
+    _, d1, q1 = ro.render_batch(m, T, K, 96)
+    np.testing.assert_array_equal(d1, d_ref)
+    assert np.abs(q1.astype(int) - q_ref.astype(int)).max() <= 1
+    # .glb: COLOR_0 on a primitive without a material (loader applies Rx(90 deg): pre-rotate the vertices back)
+    v = np.stack([s.verts[:, 0], s.verts[:, 2], -s.verts[:, 1]], 1)
+    glb = str(tmp_path / "c.glb")
+    gltf.save_glb(glb, [dict(verts=v, faces=s.faces, vcolor=np.tile(c, (len(v), 1)))])
+    g = M.load_mesh(glb)
+    assert g.parts[0]["use_vcolor"] and list(g.parts[0]["material"]) == pytest.approx([1, 1, 1, 1, 0.2, 0.8])
+    _, d2, q2 = ro.render_batch(g, T, K, 96)
+    assert ((d2 > 0) != (d_ref > 0)).mean() <= 1e-3
+    both = (d2[0] > 0) & (d_ref[0] > 0)
+    assert np.abs(q2[0][both].astype(int) - q_ref[0][both].astype(int)).max() <= 1
 
 
 def test_double_sided_material_draws_back_faces_unlit(tmp_path):
