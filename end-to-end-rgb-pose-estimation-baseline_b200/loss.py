@@ -34,10 +34,15 @@ def compute_ADD_L2_loss(TCO_gt, TCO_pred, points, use_batch_mean=True):
 
 
 def compute_angular_dist(T_CO_gt, T_CO_pred):
-    """ref: loss.py:35-43 — geodesic angle of sample 0 only; arccos is not clamped (NaN possible)."""
+    """ref: loss.py:35-43 — geodesic angle of sample 0 only; arccos is not clamped (NaN possible).
+    The value is computed in the input precision exactly as the reference does and then handed back as numpy float64.
+    test_model.py:196,208,277 multiplies it by 180/np.pi and json.dump()s it: with the float32 poses the loader produces
+    (image_dataloaders.py:75) that product was a float64 under the NumPy 1.x scalar rules the reference was written
+    for, and stays a float32 — which json refuses — under NumPy >= 2.  Widening here gives the unchanged driver the
+    NumPy 1.x result on either version (tests/test_drivers_unchanged.py::test_test_model_unchanged)."""
     R_gt = T_CO_gt[0, :3, :3].detach().cpu().numpy()
     R_pred = T_CO_pred[0, :3, :3].detach().cpu().numpy()
-    return np.arccos((np.trace(R_pred @ R_gt.T) - 1.0) / 2.0)
+    return np.float64(np.arccos((np.trace(R_pred @ R_gt.T) - 1.0) / 2.0))
 
 
 def compute_transl_dist(T_CO_gt, T_CO_pred):

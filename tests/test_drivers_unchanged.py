@@ -1,5 +1,5 @@
-"""-m gpu: the reference's OWN drivers — test_model.validate_model (test_model.py:50-110) and train_model.train
-(train_model.py:120-279, anomaly mode on, :18) — run UNMODIFIED on top of this repo's shadow modules, on a synthetic
+"""-m gpu: the reference's OWN drivers — test_model.validate_model (test_model.py:50-110), test_model.test_model
+(:112-279) and train_model.train (train_model.py:120-279, anomaly mode on, :18) — run UNMODIFIED on top of this repo's shadow modules, on a synthetic
 on-disk dataset in the layout image_dataloaders.py:70-90 reads.  This is the claim the drop-in boundary exists for
 (north_star: "train_model.py and test_model.py work unchanged").
 
@@ -196,3 +196,87 @@ def test_train_unchanged(drivers, loss):
         log = pickle.load(f)
     assert np.isfinite(log["loss"]["add_l1"]).all() and (log["loss"]["add_l1"][:3] > 0).all()
     assert len(log["val_loss"]) >= 1 and np.isfinite(log["val_loss"][0][1]).all()
+
+
+def _oracle_test(model, config):
+    """test_model's loop (test_model.py:161-214) restated over the CPU oracle at batch size 1: per class, per example,
+    per iteration ADD-L2 (loss.py:20-33, no batch mean) plus the angle / translation distance of the pose BEFORE the
+    last update (test_model.py:196-197 feeds T_CO_pred, not T_CO_pred_new)."""
+    from oracle import assemble_ref, pose_loss_ref
+    from oracle import raster_oracle as ro
+    from rac import mesh as M
+    il = sys.modules["image_dataloaders"]
+    iters = config["test_config"]["predict_iterations"]
+    rot, und = config["network"]["rotation_representation"], config["advanced"]["use_normalized_depth"]
+    out = {}
+    with torch.no_grad():
+        for cls in CLASSES:
+            _, _, loader = il.get_dataloaders(dict(config["test_dataset_config"], classes=[cls]), 1)
+            out[cls] = {"addl2": [], "angle": [], "transl": []}
+            for init_imgs, gt_imgs, T_init, T_gt, verts, mesh_paths, depths, cam_mats in loader:
+                depths, gt, T_pred, row = depths.numpy(), gt_imgs.numpy(), T_init, []
+                for j in range(iters):
+                    if j == 0:
+                        pred = init_imgs.numpy()
+                    else:
+                        pred, depths, _ = ro.render_batch_mixed([M.load_mesh(p) for p in mesh_paths], np.asarray(T_pred, np.float32),
+                                                                cam_mats.numpy().astype(np.float32), S)
+                    x = assemble_ref.prepare_model_input(pred, gt, depths, und)
+                    T_new = pose_loss_ref.pose_update(model(x.cuda()).cpu(), torch.as_tensor(T_pred), rot, cam_mats)
+                    row.append(float(pose_loss_ref.add_l2(T_gt, T_new, verts, batch_mean=False)[0]))
+                    if j == iters - 1:
+                        Rp, Rg = np.asarray(T_pred, np.float64)[0, :3, :3], T_gt.numpy()[0, :3, :3]
+                        out[cls]["angle"].append(np.degrees(np.arccos((np.trace(Rp @ Rg.T) - 1.0) / 2.0)))
+                        out[cls]["transl"].append(float(np.linalg.norm(T_gt.numpy()[0, :3, 3] - np.asarray(T_pred)[0, :3, 3])))
+                    T_pred = T_new.numpy()
+                out[cls]["addl2"].append(row)
+    return out
+
+
+def test_test_model_unchanged(drivers, capsys):
+    """test_model.test_model (test_model.py:112-279) — the third hot-loop call site, and the one that differs: batch size
+    forced to 1, a render of the GT pose first (:165), numpy cam_mats into render_batch, per-sample ADD-L1 / ADD-L2,
+    angular / translation distance on CUDA tensors, LazyArrays collected in pred_imgs_seq and handed to the figure code,
+    a final render after the loop (:214), a model loaded through fetch_network as test_model.py:296 does, and the
+    reference's only latency measurement ("avg time", :274-275)."""
+    import json
+    import rac
+    root, tm, tr = drivers
+    cfg = _config(root, "6D", "add_l1", True)
+    cfg["logging"]["logdir"] = os.path.join(root, "logdir_test_model")
+    models = sys.modules["models"]
+    torch.manual_seed(3)
+    path = os.path.join(cfg["model_io"]["model_save_dir"], "for_test_model.pth")
+    os.makedirs(os.path.dirname(path), exist_ok=True)
+    torch.save(models.fetch_network("baseline", "6D", True).state_dict(), path)
+    model = models.fetch_network("baseline", "6D", True, True, path)
+    capsys.readouterr()
+    n0 = rac.launch_count()
+    mean_last_class = tm.test_model(model, cfg)                   # the reference's function, unmodified
+    printed = capsys.readouterr().out
+    iters, n_ex = cfg["test_config"]["predict_iterations"], N_PER_SPLIT["test"]
+    # per example: 1 GT render + (iters - 1) refinement renders + 1 final render, iters input assemblies / pose updates / losses
+    assert rac.launch_count() - n0 >= len(CLASSES) * n_ex * (iters + 1) * 3
+    assert mean_last_class.shape == (iters,) and np.isfinite(mean_last_class).all()
+    avg = printed.split("avg time")[1].split()[0]
+    assert 0.0 < float(avg) < 60.0, avg                            # mean seconds per B = 1 iteration (:179,191,204-205)
+    tdir = os.path.join(cfg["logging"]["logdir"], "test", "synth-img")
+    with open(os.path.join(tdir, "results.json")) as f:
+        res = json.load(f)
+    with open(os.path.join(tdir, "results_all.json")) as f:
+        res_all = json.load(f)
+    assert os.path.isfile(os.path.join(tdir, "results.pkl"))
+    ref = _oracle_test(model.eval(), cfg)
+    for cls in CLASSES:
+        ours = np.array(res[cls])
+        assert ours.shape == (n_ex, iters) and np.isfinite(ours).all() and (ours > 0).all()
+        for k in ("angle_mean", "transl_mean", "ADDL2_mean"):
+            assert np.isfinite(res_all[cls][k]), (cls, k)
+        want = np.array(ref[cls]["addl2"])
+        # iteration 0 consumes the loader's init render (identical inputs); later ones go through the rasteriser
+        np.testing.assert_allclose(ours[:, 0], want[:, 0], rtol=2e-4)
+        np.testing.assert_allclose(ours[:, 1:], want[:, 1:], rtol=2e-2)
+        np.testing.assert_allclose(res_all[cls]["ADDL2"], want[:, -1], rtol=2e-2)
+        np.testing.assert_allclose(res_all[cls]["angle"], ref[cls]["angle"], rtol=2e-2, atol=1e-2)
+        np.testing.assert_allclose(res_all[cls]["transl"], ref[cls]["transl"], rtol=2e-2, atol=1e-4)
+    np.testing.assert_allclose(mean_last_class, np.array(res[CLASSES[-1]]).mean(0), rtol=1e-6)
