@@ -510,10 +510,13 @@ static int launch_gt_norm(const float* d_gt_hwc, float* d_x_nchw, int B, int npi
     RAC_MAX_CARVEOUT_ONCE(gt_norm_kernel);     // (rac_assemble_input reaches this kernel without render_common)
     // standalone launches (no zero-fill, one cluster per image, nothing co-resident): the bulk-copy variant
     if (vec && !zero_render_planes && n_clusters <= 0 && !d_live_loads && gt_tma_enabled()) {
-        static std::atomic<int> configured{0};
-        if (!configured.load()) {
+        static std::atomic<unsigned long long> configured{0};      // bit per device ordinal: function attributes are per device
+        int dev = 0;
+        RAC_CUDA_CHECK(cudaGetDevice(&dev));
+        const unsigned long long bit = 1ull << (dev & 63);
+        if (!(configured.load(std::memory_order_acquire) & bit)) {
             RAC_CUDA_CHECK(cudaFuncSetAttribute(gt_norm_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGtTmaSmem));
-            configured.store(1);
+            configured.fetch_or(bit, std::memory_order_release);
         }
         cudaLaunchConfig_t tc = {};
         tc.gridDim = dim3(kGtCluster, B);

@@ -35,18 +35,39 @@ def blend_imgs(im1, im2, alpha):
     return rac.blend_device(im1, im2, alpha).cpu().numpy().astype(np.float64)
 
 
+_REFERENCE_SYMBOLS = ("create_silhouette", "blend_imgs", "visualize_examples", "create_interpolated_image_fig")
+
+
 def _overlay_reference():
-    """Load the reference's visualization.py (first one on sys.path that is not this file) and re-export it."""
+    """Load the reference's visualization.py (first one on sys.path that is not this file) and re-export it.
+    A candidate is taken only if its source defines the reference module's own functions (an unrelated
+    visualization.py earlier on sys.path is never executed), and a candidate that fails to import — matplotlib, cv2
+    or the reference's `models` package missing — is reported with a warning and skipped: the two CUDA functions above
+    stay usable on their own."""
     here = os.path.dirname(os.path.abspath(__file__))
     for entry in sys.path:
         d = os.path.abspath(entry or os.getcwd())
         cand = os.path.join(d, "visualization.py")
         if d == here or not os.path.isfile(cand):
             continue
+        try:
+            with open(cand, "r", encoding="utf-8", errors="replace") as f:
+                src = f.read()
+        except OSError:
+            continue
+        if not all(("def " + name + "(") in src for name in _REFERENCE_SYMBOLS):
+            continue
         spec = importlib.util.spec_from_file_location("_reference_visualization", cand)
         ref = importlib.util.module_from_spec(spec)
         sys.modules["_reference_visualization"] = ref
-        spec.loader.exec_module(ref)
+        try:
+            spec.loader.exec_module(ref)
+        except Exception as e:      # noqa: BLE001 — any import-time failure of the plotting stack
+            sys.modules.pop("_reference_visualization", None)
+            import warnings
+            warnings.warn(f"visualization: the reference's plotting module {cand} could not be imported ({type(e).__name__}: {e}); "
+                          "only create_silhouette / blend_imgs are available", RuntimeWarning)
+            continue
         ref.create_silhouette, ref.blend_imgs = create_silhouette, blend_imgs
         for name, val in vars(ref).items():
             if not name.startswith("__") and name not in ("create_silhouette", "blend_imgs"):

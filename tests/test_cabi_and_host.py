@@ -203,3 +203,38 @@ def test_host_pack_division_free_check_equals_the_division_form(monkeypatch):
     assert verdicts["0"] == verdicts["1"]
     want = [int(any(v == c / 255.0 for c in range(256))) for v in vals]
     assert verdicts["1"] == want
+
+
+def test_visualization_overlay_ignores_strangers_and_survives_a_broken_plotting_stack(tmp_path, monkeypatch):
+    """The shadow visualization.py overlays the reference's plotting module.  An unrelated visualization.py earlier on
+    sys.path must not be executed, and a reference module whose imports fail (matplotlib / cv2 / models missing) must not
+    take create_silhouette / blend_imgs down with it."""
+    import importlib
+    import sys
+    import warnings
+    stranger = tmp_path / "stranger"
+    stranger.mkdir()
+    (stranger / "visualization.py").write_text("raise SystemExit('an unrelated visualization.py was executed')\n")
+    broken = tmp_path / "broken"
+    broken.mkdir()
+    (broken / "visualization.py").write_text(
+        "import a_plotting_package_that_is_not_installed\n"
+        "def create_silhouette(img, silhouette_only=False): pass\n"
+        "def blend_imgs(im1, im2, alpha): pass\n"
+        "def visualize_examples(model, config, t): pass\n"
+        "def create_interpolated_image_fig(a, b, c): pass\n")
+    pkg = os.path.join(ROOT, "end-to-end-rgb-pose-estimation-baseline_b200")
+    saved = {k: sys.modules.pop(k) for k in ("visualization", "_reference_visualization") if k in sys.modules}
+    monkeypatch.setattr(sys, "path", [pkg, str(stranger), str(broken)] +
+                        [p for p in sys.path if not os.path.isfile(os.path.join(p or ".", "visualization.py"))])
+    try:
+        with warnings.catch_warnings(record=True) as w:
+            warnings.simplefilter("always")
+            viz = importlib.import_module("visualization")
+        assert viz.__file__.startswith(pkg)
+        assert viz._reference is None and callable(viz.create_silhouette) and callable(viz.blend_imgs)
+        assert any("could not be imported" in str(x.message) for x in w)
+        assert "_reference_visualization" not in sys.modules
+    finally:
+        sys.modules.pop("visualization", None)
+        sys.modules.update(saved)
