@@ -371,26 +371,63 @@ class DeviceMesh:
 # Path / object -> uploaded mesh, least recently used first.  The reference re-parses the file for every image and keeps
 # nothing; training draws from thousands of distinct ModelNet10 files (roughly 4.7 k across train + validation), more
 # than the library's device table holds (kMaxMeshes = 4096, rac_common.cuh), so the cache is BOUNDED: beyond
-# MAX_DEVICE_MESHES entries the least recently used mesh is destroyed (rac_mesh_destroy synchronises the device first:
-# a batch in flight may still read it) and simply uploaded again if it is ever drawn again.
+# MAX_DEVICE_MESHES entries the least recently used meshes are destroyed and simply uploaded again if they are ever
+# drawn again.  Rules of eviction:
+#   * only meshes nobody else holds: a DeviceMesh a caller still references (rac.RenderCompareStep.meshes, a captured
+#     graph's owner — mesh ids are baked into graphs by value, and a freed slot is reused by the next upload) is
+#     skipped, so a handle stays valid for as long as its DeviceMesh object is alive outside the cache;
+#   * never while the current stream is capturing (rac_mesh_destroy synchronises the device — a batch in flight may still
+#     read the mesh — which is illegal under capture): the cache overshoots instead, the device table has 4x the room;
+#   * _EVICT_BATCH victims at a time, so the device-wide synchronise is paid once per batch of evictions, not per mesh
+#     (the second and later destroys of a batch find the device idle).
 import collections
+import sys
 
 MAX_DEVICE_MESHES = 1024
 MAX_HOST_MESHES = 4096
+_EVICT_BATCH = 64
 _cache = collections.OrderedDict()
 _cache_lock = threading.Lock()
 _host_cache = collections.OrderedDict()
 
 
-def _cache_get(key, make):
-    """LRU lookup / insert under _cache_lock (the caller holds it)."""
+def _capturing():
+    try:
+        import torch
+        return torch.cuda.is_available() and torch.cuda.is_current_stream_capturing()
+    except Exception:
+        return False
+
+
+def _unheld_refcount():
+    """sys.getrefcount of a value that only a dict holds, measured the way _evict_lru asks (interpreter-version proof)."""
+    d = {0: object()}
+    return sys.getrefcount(d[0])
+
+
+_UNHELD = _unheld_refcount()
+
+
+def _evict_lru():
+    victims = []
+    for k in _cache:                              # keys, least recently used first (no loop variable holds a value)
+        if sys.getrefcount(_cache[k]) <= _UNHELD: # only the cache references it
+            victims.append(k)
+            if len(victims) >= _EVICT_BATCH:
+                break
+    for k in victims:
+        _cache.pop(k).destroy()
+
+
+def _cache_get(key, make, owner=None):
+    """LRU lookup / insert under _cache_lock (the caller holds it).  owner: the host Mesh of an ("obj", id) key; the
+    DeviceMesh keeps it alive (dm.mesh), so its id() cannot be recycled while the entry exists — checked all the same."""
     dm = _cache.get(key)
-    if dm is not None:
+    if dm is not None and (owner is None or dm.mesh is owner):
         _cache.move_to_end(key)
         return dm
-    while len(_cache) >= MAX_DEVICE_MESHES:
-        _, old = _cache.popitem(last=False)
-        old.destroy()
+    if len(_cache) >= MAX_DEVICE_MESHES and not _capturing():
+        _evict_lru()
     dm = _cache[key] = make()
     return dm
 
@@ -415,7 +452,7 @@ def device_mesh(path_or_mesh):
         return path_or_mesh
     if isinstance(path_or_mesh, Mesh):
         with _cache_lock:
-            return _cache_get(("obj", id(path_or_mesh)), lambda: DeviceMesh(path_or_mesh))
+            return _cache_get(("obj", id(path_or_mesh)), lambda: DeviceMesh(path_or_mesh), owner=path_or_mesh)
     key = os.path.abspath(path_or_mesh)
     hm = host_mesh(key)
     with _cache_lock:

@@ -238,3 +238,32 @@ def test_visualization_overlay_ignores_strangers_and_survives_a_broken_plotting_
     finally:
         sys.modules.pop("visualization", None)
         sys.modules.update(saved)
+
+
+def test_mesh_cache_evicts_only_unreferenced_entries_in_batches(monkeypatch):
+    """Eviction rules of rac/mesh.py's device cache, on stand-in entries (no GPU): entries somebody outside the cache
+    still references survive, the others go least-recently-used first, _EVICT_BATCH at a time."""
+    from rac import mesh as M
+
+    class Entry:
+        def __init__(self):
+            self.destroyed = False
+            self.mesh = None
+
+        def destroy(self):
+            self.destroyed = True
+
+    monkeypatch.setattr(M, "_cache", type(M._cache)())
+    monkeypatch.setattr(M, "MAX_DEVICE_MESHES", 8)
+    monkeypatch.setattr(M, "_EVICT_BATCH", 3)
+    held = [M._cache_get(k, Entry) for k in ("a", "b")]
+    for i in range(20):
+        M._cache_get(i, Entry)
+        assert len(M._cache) <= 8
+    assert [e.destroyed for e in held] == [False, False] and list(M._cache)[:2] == ["a", "b"]
+    assert M._cache_get("a", Entry) is held[0] and list(M._cache)[-1] == "a"        # a hit refreshes the entry
+    survivors = [k for k in M._cache if isinstance(k, int)]
+    assert survivors == sorted(survivors) and survivors[-1] == 19 and len(survivors) <= 6
+    # everything pinned: the cache overshoots rather than destroying a mesh in use
+    pinned = [M._cache_get(("p", i), Entry) for i in range(12)]
+    assert not any(e.destroyed for e in pinned + held)

@@ -103,6 +103,36 @@ def test_device_mesh_cache_is_bounded(monkeypatch):
     M.clear_cache()
 
 
+def test_device_mesh_held_by_a_caller_is_never_evicted():
+    """A DeviceMesh somebody still references (rac.RenderCompareStep.meshes, the owner of a captured graph: mesh ids are
+    baked into graphs by value and a freed table slot is reused by the next upload) survives any amount of cache
+    churn with its handle intact; unreferenced entries around it are evicted in batches."""
+    import ctypes
+    import rac
+    from rac import _lib, mesh as M
+    M.clear_cache()
+    rng = np.random.default_rng(1)
+    B, S = 64, 64
+    base = M.box(0.5, 0.4, 0.3, 1)
+    mk = lambda: M.Mesh(base.verts * np.float32(0.6 + 0.8 * rng.uniform()), base.faces)
+    T, _ = sample_poses(B, seed=4)
+    K = intrinsics(B, S, S)
+    held_host = [mk() for _ in range(B)]
+    held = [M.device_mesh(m) for m in held_host]                 # what a loop-owning caller keeps
+    handles = [d.handle for d in held]
+    first = rac.render_batch_device(T, held, K, S, want_rgb=False)["depth"].clone()
+    for _ in range(0, M.MAX_DEVICE_MESHES + 4 * B, B):           # churn well past the bound
+        rac.render_batch_device(T, [mk() for _ in range(B)], K, S, want_rgb=False)
+    assert len(M._cache) <= M.MAX_DEVICE_MESHES
+    v, t = ctypes.c_int(), ctypes.c_int()
+    for d, h in zip(held, handles):
+        assert d.handle == h and M._cache.get(("obj", id(d.mesh))) is d
+        assert _lib.lib().rac_mesh_info(h, ctypes.byref(v), ctypes.byref(t)) == 0 and (v.value, t.value) == (d.V, d.T)
+    assert torch.equal(first, rac.render_batch_device(T, held, K, S, want_rgb=False)["depth"])
+    del held, d
+    M.clear_cache()
+
+
 def test_double_sided_open_mesh_matches_oracle(tmp_path):
     """An OPEN textured surface (a bumpy sphere with 40 % of its faces removed) whose material is doubleSided: through the
     holes the inside of the far wall is visible — drawn back faces, unlit, with the right texture coordinates (the
