@@ -434,6 +434,29 @@ def run_ours(args):
     eb_ms, eb_wall_ms = timed(step_e2e_batch, nb_batches)
     eb_ms = max(eb_ms, eb_wall_ms)
 
+    # secondary: the reference's own latency figure — test_model.py:179-205,274-275 times, at batch size 1 and with
+    # time.time(), render_batch -> torch.tensor(T).to(device) -> prepare_model_input -> model -> calculate_T_CO_pred and
+    # prints the mean as "avg time".  Same calls, same input types, same clock; the CNN (not this repo's) is replaced by
+    # the fixed head output, so this is the hot path's share of that figure.
+    import time as _time
+    s0 = dsets[0]
+    gt1, K1, paths1 = s0["np_gt_f64"][:1].copy(), Ks_f64[:1].numpy(), mesh_paths[:1]
+    y1 = s0["h_y"][:1]
+    lat = []
+    with torch.no_grad():
+        T1 = s0["T_init_f64"][:1].numpy().astype(np.float32)
+        for it in range(3 + 30):
+            t0 = _time.time()
+            imgs1, depths1 = DL.render_batch(T1, paths1, K1, (W, H), False)                                  # test_model.py:186
+            T1d = torch.tensor(T1).to(dev)                                                                    # :187
+            x1 = DL.prepare_model_input(imgs1, gt1, depths1, False).to(dev)                                   # :189
+            T1n = RR.calculate_T_CO_pred(y1.to(dev), T1d, ROT, torch.as_tensor(K1))                           # :191
+            t1 = _time.time()
+            T1 = T1n.detach().cpu().numpy()                                                                   # :202
+            if it >= 3:
+                lat.append(t1 - t0)
+    latency_b1_ms = 1e3 * float(np.mean(lat))
+
     per_step = ms / args.steps
     value = world * B * args.steps / (ms * 1e-3)
     algo_bytes = 36.0 * W * H * B + (12.0 * len(mesh.verts) + 12.0 * len(mesh.faces)) + 100.0 * B
@@ -449,18 +472,20 @@ def run_ours(args):
     # field is null when the sources in the tree differ.
     traffic, traffic_rev, traffic_note = None, None, "no capture committed"
     lib_digest = stage_source_digest()
-    try:
-        with open(os.path.join(ROOT, "profiles", "traffic_r02.json")) as f:
-            tj = json.load(f)
+    for tname in ("traffic_r03.json", "traffic_r02.json"):       # newest capture first
+        try:
+            with open(os.path.join(ROOT, "profiles", tname)) as f:
+                tj = json.load(f)
+        except Exception:
+            continue
         traffic_rev = tj.get("lib_digest")
         if traffic_rev and lib_digest and traffic_rev == lib_digest:
             traffic = float(tj["stage_dram_bytes_per_call"])
-            traffic_note = ("profiles/traffic_r02.json: ncu dram__bytes_read+write summed over the stage's kernels, per call "
-                            "(serialised capture, so part of the 118 MB written is still dirty in the 126 MB L2 when the last kernel ends)")
+            traffic_note = ("profiles/%s: ncu dram__bytes_read+write summed over the stage's kernels, per call "
+                            "(serialised capture, so part of the 118 MB written is still dirty in the 126 MB L2 when the last kernel ends)" % tname)
         else:
-            traffic_note = "profiles/traffic_r02.json was captured on stage sources %s, this tree has %s: stale, not reported" % (traffic_rev, lib_digest)
-    except Exception:
-        pass
+            traffic_note = "profiles/%s was captured on stage sources %s, this tree has %s: stale, not reported" % (tname, traffic_rev, lib_digest)
+        break
     achieved = algo_bytes / (stage_ms * 1e-3) / 1e9
     small_h2d = sum(dsets[0][k].numel() * 4 for k in ("h_T_init", "h_T_gt", "h_y", "h_pts"))
     h2d = small_h2d + dsets[0]["h_gt"].numel() * 4
@@ -509,6 +534,10 @@ def run_ours(args):
                       "ms_per_batch": eb_ms / nb_batches, "iters_per_batch": ITERS_PER_BATCH, "batches": nb_batches,
                       "h2d_bytes_per_batch": h2d + (ITERS_PER_BATCH - 1) * (B * 64 + B * 9 * 4), "d2h_bytes_per_batch": ITERS_PER_BATCH * (B * 64 + 4),
                       "note": "secondary (round 1): the loop shape on pinned float32 crops, gt uploaded and normalised once per batch"},
+        "latency_b1": {"value": latency_b1_ms, "unit": "ms per iteration at batch size 1 (host wall clock, time.time())", "iters": len(lat),
+                       "note": "secondary: the quantity test_model.py:179-205 measures and :274-275 prints as 'avg time' — render_batch -> torch.tensor(T).to(device) "
+                               "-> prepare_model_input -> calculate_T_CO_pred through the reference-named calls at B = 1, CNN excluded (fixed head output); "
+                               "like the reference's figure it stops the clock without synchronising the device"},
         "gpu_launches": int(launches), "clocks": clocks,
     }
     if rank == 0:
